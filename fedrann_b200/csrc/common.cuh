@@ -1,0 +1,99 @@
+// Shared declarations of the fedrann_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/fedrann_b200.h"
+
+#define FR_EMPTY_KEY 0xFFFFFFFFFFFFFFFFull
+#define FR_HASH_MUL 0x9E3779B97F4A7C15ull
+
+// Device-side view of the k-mer lookup structure (K2 builds it, K3 probes it).
+//  * bloom: blocked Bloom filter, one 32-bit block per probe (1 L2 sector),
+//    3 bits per key, sized 16-32 bits per key so it stays L2-resident.
+//  * keys/vals: open-addressing table (linear probing, <= 50 % load), only
+//    touched by the few percent of probes that pass the filter.
+struct FrTable {
+    const uint32_t *bloom;
+    const uint64_t *keys;
+    const uint32_t *vals;
+    int lg_words;  // log2(#bloom words)
+    int lg_cap;    // log2(#table slots)
+    int k;
+    int64_t n;     // number of features F
+};
+
+struct fr_ctx {
+    int device = 0;
+    int sm_count = 148;
+    std::string err;
+    int64_t launches = 0;
+
+    // K2
+    uint32_t *d_bloom = nullptr;
+    uint64_t *d_keys = nullptr;
+    uint32_t *d_vals = nullptr;
+    FrTable table{};
+    bool has_table = false;
+
+    // K3 scratch (kept between calls, grown on demand)
+    int32_t *d_scratch = nullptr;   // per-read sorted unique hits, bump-allocated
+    int64_t scratch_cap = 0;
+    uint32_t *d_spill = nullptr;    // overflow hit lists for very long reads
+    int64_t spill_cap = 0;
+    int64_t *d_read_off = nullptr;  // [n_reads] offset into d_scratch
+    int32_t *d_read_cnt = nullptr;  // [n_reads]
+    int64_t reads_cap = 0;
+    unsigned long long *d_counters = nullptr;  // [0] scratch used, [1] spill used, [2] flags
+    unsigned long long *h_counters = nullptr;  // pinned mirror
+    int64_t *d_scan_tmp = nullptr;
+    int64_t scan_tmp_cap = 0;
+    // state of the last fr_extract_count
+    int64_t last_n_reads = -1;
+    const int64_t *last_indptr = nullptr;
+
+    // K6/K7 scratch
+    void *d_knn_ws = nullptr;
+    int64_t knn_ws_cap = 0;
+    int64_t knn_fallback_rows = 0;
+};
+
+int fr_fail(fr_ctx *ctx, int code, const char *what);
+int fr_cuda_fail(fr_ctx *ctx, cudaError_t e, const char *what);
+int fr_ensure(fr_ctx *ctx, void **ptr, int64_t *cap, int64_t need_bytes, const char *what);
+
+#define FR_CUDA(ctx, call)                                       \
+    do {                                                         \
+        cudaError_t _e = (call);                                 \
+        if (_e != cudaSuccess) return fr_cuda_fail(ctx, _e, #call); \
+    } while (0)
+
+#define FR_LAUNCH_CHECK(ctx, name)                               \
+    do {                                                         \
+        (ctx)->launches++;                                       \
+        cudaError_t _e = cudaGetLastError();                     \
+        if (_e != cudaSuccess) return fr_cuda_fail(ctx, _e, name); \
+    } while (0)
+
+__device__ __forceinline__ uint64_t fr_hash(uint64_t kmer) {
+    return (kmer ^ (kmer >> 29)) * FR_HASH_MUL;
+}
+__device__ __forceinline__ uint32_t fr_bloom_word(uint64_t h, int lg_words) {
+    return (uint32_t)(h >> (64 - lg_words));
+}
+__device__ __forceinline__ uint32_t fr_bloom_mask(uint64_t h) {
+    uint32_t lo = (uint32_t)h;
+    return (1u << (lo >> 27)) | (1u << ((lo >> 22) & 31)) | (1u << ((lo >> 17) & 31));
+}
+__device__ __forceinline__ uint32_t fr_table_slot(uint64_t h, int lg_cap) {
+    return (uint32_t)(h >> (64 - lg_cap));
+}
+
+// internal launchers (defined in the .cu files)
+int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,
+                      int64_t n_reads, uint32_t *d_docfreq, cudaStream_t st);
+int fr_scan_counts(fr_ctx *ctx, const int32_t *d_cnt, int64_t n, int64_t *d_indptr, cudaStream_t st);
+int fr_gather_rows(fr_ctx *ctx, int32_t *d_indices, cudaStream_t st);
+int fr_docfreq_launch(fr_ctx *ctx, int64_t nnz, uint32_t *d_docfreq, cudaStream_t st);

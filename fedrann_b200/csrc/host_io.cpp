@@ -1,0 +1,161 @@
+// Native host-side I/O of the path: the k-mer library parser, the FASTA/FASTQ
+// reader and the output.bin / kmer_frequency.bin writers.  These restate the
+// host parts of kmer_searcher.cpp (library load :259-273, read_sequences
+// :153-201, write_to_file :98-130, writeKmerStatsToBinary :203-229) so that the
+// replacement executable and the Python host share one implementation.
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_set>
+#include <vector>
+
+#include "../../include/fedrann_b200.h"
+
+namespace {
+inline bool is_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f'; }
+
+inline int base_code(char c) {
+    switch (c) {
+        case 'A': case 'a': return 0;
+        case 'C': case 'c': return 1;
+        case 'G': case 'g': return 2;
+        case 'T': case 't': return 3;
+        default: return -1;
+    }
+}
+}  // namespace
+
+extern "C" int fr_library_parse(const char *text, int64_t text_len, int k, uint64_t *codes_out, int64_t cap,
+                                int64_t *n_out) {
+    if (!text || text_len < 0 || k < 1 || k > 31 || !n_out) return FR_ERR_ARG;
+    std::unordered_set<uint64_t> seen;
+    seen.reserve((size_t)(text_len / (k + 1)) + 16);
+    int64_t n = 0, i = 0;
+    while (i < text_len) {
+        while (i < text_len && is_space(text[i])) ++i;
+        if (i >= text_len) break;
+        const int64_t s = i;
+        while (i < text_len && !is_space(text[i])) ++i;
+        if (i - s != k) continue;                      // :266 wrong length
+        uint64_t code = 0;
+        bool ok = true;
+        for (int64_t j = s; j < i; ++j) {
+            int c = base_code(text[j]);
+            if (c < 0) { ok = false; break; }          // :147 non-ACGT
+            code = (code << 2) | (uint64_t)c;
+        }
+        if (!ok) continue;
+        if (!seen.insert(code).second) continue;       // :268 duplicate
+        if (codes_out && n < cap) codes_out[n] = code;
+        ++n;
+    }
+    *n_out = n;
+    return FR_OK;
+}
+
+extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64_t *offsets_out,
+                              char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len) {
+    if (!text || text_len < 0 || !n_reads || !n_bases || !names_len) return FR_ERR_ARG;
+    const bool emit = bases_out != nullptr;
+    int64_t R = 0, B = 0, NL = 0;
+    bool checked = false, is_fastq = false;
+    bool have_rec = false;  // FASTA: a record with a non-empty id is open
+    int64_t pos = 0;
+    auto next_line = [&](int64_t &ls, int64_t &le) -> bool {
+        if (pos >= text_len) return false;
+        ls = pos;
+        const void *nl = memchr(text + pos, '\n', (size_t)(text_len - pos));
+        le = nl ? (const char *)nl - text : text_len;
+        pos = nl ? le + 1 : text_len;
+        return true;
+    };
+    auto open_rec = [&](const char *id, int64_t idlen) {
+        if (emit) {
+            offsets_out[R] = B;
+            memcpy(names_out + NL, id, (size_t)idlen);
+            names_out[NL + idlen] = '\n';
+        }
+        NL += idlen + 1;
+    };
+    int64_t ls, le;
+    if (emit) offsets_out[0] = 0;
+    while (next_line(ls, le)) {
+        if (!checked) { is_fastq = le > ls && text[ls] == '@'; checked = true; }   // :163-166
+        if (le == ls) continue;                                                     // :168
+        if (!is_fastq) {
+            if (text[ls] == '>') {
+                if (have_rec) { ++R; have_rec = false; }
+                int64_t idend = ls + 1;
+                while (idend < le && text[idend] != ' ' && text[idend] != '\t') ++idend;   // :176-181
+                if (idend > ls + 1) { open_rec(text + ls + 1, idend - ls - 1); have_rec = true; }
+            } else if (have_rec) {
+                if (emit) memcpy(bases_out + B, text + ls, (size_t)(le - ls));      // :185
+                B += le - ls;
+            }
+        } else if (text[ls] == '@') {                                               // :188-194
+            open_rec(text + ls + 1, le - ls - 1);
+            int64_t ss, se;
+            if (next_line(ss, se)) {
+                if (emit) memcpy(bases_out + B, text + ss, (size_t)(se - ss));
+                B += se - ss;
+            }
+            int64_t a, b;
+            next_line(a, b);
+            next_line(a, b);
+            ++R;
+        }
+    }
+    if (!is_fastq && have_rec) ++R;
+    if (emit) offsets_out[R] = B;
+    *n_reads = R; *n_bases = B; *names_len = NL;
+    return FR_OK;
+}
+
+extern "C" int fr_write_output_bin(const char *path, const char *names, const int64_t *name_offsets, int64_t n_reads,
+                                   const int64_t *indptr, const int32_t *indices) {
+    FILE *f = fopen(path, "wb");
+    if (!f) return FR_ERR_ARG;
+    std::vector<char> buf;
+    buf.reserve(1 << 22);
+    auto put = [&](const void *p, size_t n) {
+        const char *c = (const char *)p;
+        buf.insert(buf.end(), c, c + n);
+        if (buf.size() >= (1u << 22)) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
+    };
+    const char magic[8] = {'K', 'M', 'E', 'R', 1, 0, 0, 0};
+    put(magic, 8);
+    uint64_t total = (uint64_t)n_reads;
+    put(&total, 8);
+    int rc = FR_OK;
+    for (int64_t r = 0; r < n_reads && rc == FR_OK; ++r) {
+        const char *id = names + name_offsets[r];
+        const int64_t idlen = name_offsets[r + 1] - name_offsets[r];
+        for (int64_t j = 0; j < idlen; ++j)
+            if (id[j] < 32 || id[j] > 126) rc = FR_ERR_ARG;       // :112-116 (the reference throws)
+        uint16_t l16 = (uint16_t)idlen;
+        put(&l16, 2);
+        put(id, (size_t)idlen);
+        uint32_t cnt = (uint32_t)(indptr[r + 1] - indptr[r]);
+        put(&cnt, 4);
+        for (int64_t t = indptr[r]; t < indptr[r + 1]; ++t) {
+            uint64_t v = (uint64_t)(uint32_t)indices[t];
+            put(&v, 8);
+        }
+    }
+    if (!buf.empty()) fwrite(buf.data(), 1, buf.size(), f);
+    fclose(f);
+    return rc;
+}
+
+extern "C" int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features) {
+    FILE *f = fopen(path, "wb");
+    if (!f) return FR_ERR_ARG;
+    for (int64_t i = 0; i < n_features; ++i) {
+        if (!docfreq[i]) continue;                                   // :217
+        uint64_t rec[2] = {(uint64_t)i, (uint64_t)docfreq[i]};
+        fwrite(rec, 8, 2, f);
+    }
+    fclose(f);
+    return FR_OK;
+}

@@ -1,0 +1,30 @@
+// fr_knn dispatcher: tensor-core candidate pass + exact re-rank (mode 0) or the
+// exact fp32 scan (mode 1).  Replaces NNDescent_ava.get_neighbors
+// (nearest_neighbors.py:22-55) with an exact search.
+#include "common.cuh"
+
+int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
+                        int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
+                        int32_t *d_idx, float *d_dist, cudaStream_t st);
+int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
+                     int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st);
+
+extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
+                      int Dp, int64_t q0, int64_t nq, int k, int mode, int32_t *d_idx, float *d_dist,
+                      void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    if (!d_En || !d_norms || !d_idx || !d_dist || n_db < 0 || nq < 0 || q0 < 0 || q0 + nq > n_db || D <= 0)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_knn: bad argument");
+    if (nq == 0) return FR_OK;
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    ctx->knn_fallback_rows = 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mode == 1)
+        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
+    if (mode != 0) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode must be 0 or 1");
+    if (!d_Eh || Dp < D || (Dp % 64) != 0)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode 0 needs the fp16 copy with Dp % 64 == 0");
+    return fr_knn_tc_launch(ctx, d_En, d_Eh, d_norms, n_db, D, Dp, q0, nq, k, d_idx, d_dist, st);
+}
+
+extern "C" int64_t fr_knn_last_fallback_rows(const fr_ctx *ctx) { return ctx ? ctx->knn_fallback_rows : 0; }

@@ -1,0 +1,158 @@
+// K5 (normalise) and the exact fp32 cosine-kNN scan.
+//
+// The scan is the arithmetic definition of the path's answer ("the reference's
+// kNN backend in exact mode", nearest_neighbors.py:22-55 with metric="cosine";
+// SURVEY.md 8(c)): dist = 1 - <x/|x|, y/|y|> in fp32, ascending, ties by lower
+// index, zero-norm rows at distance 1 from everything.  It serves fr_knn
+// mode 1 and the rows the tensor-core path (knn_tc.cu) cannot certify.
+#include "common.cuh"
+
+// ---- K5: one warp per row ----
+__global__ void fr_normalize_kernel(const float *__restrict__ E, int64_t N, int D, int Dp,
+                                    float *__restrict__ En, __half *__restrict__ Eh,
+                                    float *__restrict__ norms) {
+    const int lane = threadIdx.x & 31;
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; r < N; r += nwarps) {
+        const float *x = E + r * D;
+        float s = 0.0f;
+        for (int j = lane; j < D; j += 32) { float v = x[j]; s = fmaf(v, v, s); }
+        for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
+        const float nrm = sqrtf(s);
+        const float inv = nrm > 0.0f ? 1.0f / nrm : 0.0f;
+        if (lane == 0 && norms) norms[r] = nrm;
+        for (int j = lane; j < Dp; j += 32) {
+            float v = j < D ? x[j] * inv : 0.0f;
+            if (j < D && En) En[r * D + j] = v;
+            if (Eh) Eh[r * (int64_t)Dp + j] = __float2half_rn(v);
+        }
+    }
+}
+
+extern "C" int fr_normalize(fr_ctx *ctx, const float *d_E, int64_t N, int D, int Dp, float *d_En, void *d_Eh,
+                            float *d_norms, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    if (N < 0 || D <= 0 || Dp < D || (d_Eh && (Dp % 64) != 0))
+        return fr_fail(ctx, FR_ERR_ARG, "fr_normalize: need D > 0, Dp >= D, Dp % 64 == 0");
+    if (N == 0) return FR_OK;
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    int64_t blocks = (N * 32 + 255) / 256;
+    if (blocks > (int64_t)ctx->sm_count * 32) blocks = (int64_t)ctx->sm_count * 32;
+    fr_normalize_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_E, N, D, Dp, d_En, (__half *)d_Eh,
+                                                                           d_norms);
+    FR_LAUNCH_CHECK(ctx, "fr_normalize_kernel");
+    return FR_OK;
+}
+
+// ---- exact scan: one warp = FR_QPW query rows against the whole database ----
+#define FR_QPW 4
+#define FR_EX_WARPS 4
+#define FR_MAX_K 128
+
+// sorted insertion into a warp-private list (dist asc, then idx asc); entries beyond k dropped
+__device__ __forceinline__ void fr_list_insert(float *ld, int *li, int k, float d, int idx) {
+    const int lane = threadIdx.x & 31;
+    // position = number of entries ordered before (d, idx); db is scanned in ascending idx so
+    // equal distances already in the list stay in front
+    int pos = 0;
+    for (int j = lane; j < k; j += 32) pos += (ld[j] <= d) ? 1 : 0;
+    for (int s = 16; s > 0; s >>= 1) pos += __shfl_xor_sync(0xFFFFFFFFu, pos, s);
+    if (pos >= k) return;
+    // shift [pos, k-1) right by one, back to front in 32-wide waves
+    for (int hi = k - 1; hi > pos; hi -= 32) {
+        int j = hi - lane;
+        float td = 0.f; int ti = 0;
+        bool mv = j > pos;
+        if (mv) { td = ld[j - 1]; ti = li[j - 1]; }
+        __syncwarp();
+        if (mv) { ld[j] = td; li[j] = ti; }
+        __syncwarp();
+    }
+    if (lane == 0) { ld[pos] = d; li[pos] = idx; }
+    __syncwarp();
+}
+
+// rows == nullptr: queries are q0 + [0, nq).  Otherwise rows[i] (local query index) for i < *n_rows.
+__global__ void __launch_bounds__(FR_EX_WARPS * 32)
+fr_knn_exact_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D,
+                    int64_t q0, int64_t nq, int k, const int32_t *__restrict__ rows,
+                    const unsigned long long *__restrict__ n_rows, int32_t *__restrict__ out_idx,
+                    float *__restrict__ out_dist) {
+    extern __shared__ __align__(16) unsigned char fr_ex_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *qbuf = reinterpret_cast<float *>(fr_ex_smem) + (size_t)warp * FR_QPW * D;
+    float *ld = reinterpret_cast<float *>(fr_ex_smem) + (size_t)FR_EX_WARPS * FR_QPW * D +
+                (size_t)warp * FR_QPW * FR_MAX_K;
+    int *li = reinterpret_cast<int *>(reinterpret_cast<float *>(fr_ex_smem) + (size_t)FR_EX_WARPS * FR_QPW * D +
+                                      (size_t)FR_EX_WARPS * FR_QPW * FR_MAX_K) +
+              (size_t)warp * FR_QPW * FR_MAX_K;
+    const int64_t total = rows ? (int64_t)(*n_rows) : nq;
+    const int64_t ngroups = (total + FR_QPW - 1) / FR_QPW;
+    for (int64_t g = (int64_t)blockIdx.x * FR_EX_WARPS + warp; g < ngroups; g += (int64_t)gridDim.x * FR_EX_WARPS) {
+        int64_t qloc[FR_QPW];
+        float qn[FR_QPW], worst[FR_QPW];
+#pragma unroll
+        for (int u = 0; u < FR_QPW; ++u) {
+            int64_t i = g * FR_QPW + u;
+            qloc[u] = i < total ? (rows ? (int64_t)rows[i] : i) : -1;
+            qn[u] = qloc[u] >= 0 ? norms[q0 + qloc[u]] : 0.0f;
+            for (int j = lane; j < D; j += 32)
+                qbuf[u * D + j] = qloc[u] >= 0 ? En[(q0 + qloc[u]) * D + j] : 0.0f;
+            for (int j = lane; j < k; j += 32) { ld[u * FR_MAX_K + j] = INFINITY; li[u * FR_MAX_K + j] = -1; }
+            worst[u] = INFINITY;
+        }
+        __syncwarp();
+        for (int64_t c = 0; c < n_db; ++c) {
+            const float *y = En + c * D;
+            float acc[FR_QPW];
+#pragma unroll
+            for (int u = 0; u < FR_QPW; ++u) acc[u] = 0.0f;
+            for (int j = lane; j < D; j += 32) {
+                const float yv = __ldg(&y[j]);
+#pragma unroll
+                for (int u = 0; u < FR_QPW; ++u) acc[u] = fmaf(qbuf[u * D + j], yv, acc[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < FR_QPW; ++u)
+                for (int s = 16; s > 0; s >>= 1) acc[u] += __shfl_xor_sync(0xFFFFFFFFu, acc[u], s);
+            const float cn = norms[c];
+#pragma unroll
+            for (int u = 0; u < FR_QPW; ++u) {
+                if (qloc[u] < 0) continue;
+                const float d = (qn[u] == 0.0f || cn == 0.0f) ? 1.0f : 1.0f - acc[u];
+                if (d < worst[u]) {  // warp-uniform
+                    fr_list_insert(ld + u * FR_MAX_K, li + u * FR_MAX_K, k, d, (int)c);
+                    worst[u] = ld[u * FR_MAX_K + k - 1];
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < FR_QPW; ++u) {
+            if (qloc[u] < 0) continue;
+            for (int j = lane; j < k; j += 32) {
+                out_idx[qloc[u] * k + j] = li[u * FR_MAX_K + j];
+                out_dist[qloc[u] * k + j] = ld[u * FR_MAX_K + j];
+            }
+        }
+        __syncwarp();
+    }
+}
+
+int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
+                        int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
+                        int32_t *d_idx, float *d_dist, cudaStream_t st) {
+    if (k < 1 || k > FR_MAX_K) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: k must be in [1,128]");
+    size_t smem = (size_t)FR_EX_WARPS * FR_QPW * D * sizeof(float) +
+                  (size_t)FR_EX_WARPS * FR_QPW * FR_MAX_K * (sizeof(float) + sizeof(int));
+    if (smem > 200 * 1024) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: D too large for the exact scan");
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t groups = (nq + FR_QPW - 1) / FR_QPW;
+    int64_t blocks = (groups + FR_EX_WARPS - 1) / FR_EX_WARPS;
+    if (blocks > (int64_t)ctx->sm_count * 8) blocks = (int64_t)ctx->sm_count * 8;
+    if (blocks < 1) blocks = 1;
+    fr_knn_exact_kernel<<<(unsigned)blocks, FR_EX_WARPS * 32, smem, st>>>(d_En, d_norms, n_db, D, q0, nq, k, d_rows,
+                                                                          d_n_rows, d_idx, d_dist);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_exact_kernel");
+    return FR_OK;
+}

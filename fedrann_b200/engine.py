@@ -1,0 +1,186 @@
+"""Device engine: one `Engine` per GPU (per rank) over the C ABI.
+
+PyTorch is used for device memory, streams and (in parallel.py) NCCL only;
+every computation is a kernel of libfedrann_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FedrannError, check
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ---------------------------------------------------------------------------
+# host-side parsers / writers (native, shared with the kmer_searcher tool)
+# ---------------------------------------------------------------------------
+def parse_library(text: bytes, k: int) -> np.ndarray:
+    """kmer_searcher.cpp:259-273 -> uint64 codes, index = first-occurrence rank."""
+    L = _lib.lib()
+    cap = len(text) // 2 + 1
+    codes = np.zeros(cap, dtype=np.uint64)
+    n = C.c_int64(0)
+    check(None, L.fr_library_parse(text, len(text), k, codes.ctypes.data_as(C.c_void_p), cap, C.byref(n)),
+          "fr_library_parse")
+    return codes[: n.value].copy()
+
+
+def parse_fastx(text: bytes):
+    """kmer_searcher.cpp:153-201 -> (bases uint8, offsets int64[R+1], names list)."""
+    L = _lib.lib()
+    nr, nb, nl = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    check(None, L.fr_fastx_parse(text, len(text), None, None, None, C.byref(nr), C.byref(nb), C.byref(nl)),
+          "fr_fastx_parse")
+    bases = np.zeros(max(nb.value, 1), dtype=np.uint8)
+    offsets = np.zeros(nr.value + 1, dtype=np.int64)
+    names = np.zeros(max(nl.value, 1), dtype=np.uint8)
+    check(None, L.fr_fastx_parse(text, len(text), bases.ctypes.data_as(C.c_void_p),
+                                 offsets.ctypes.data_as(C.c_void_p), names.ctypes.data_as(C.c_void_p),
+                                 C.byref(nr), C.byref(nb), C.byref(nl)), "fr_fastx_parse")
+    name_list = names[: nl.value].tobytes().decode("utf-8", "replace").split("\n")[:-1] if nl.value else []
+    return bases[: nb.value], offsets, name_list
+
+
+def write_output_bin(path: str, names, indptr: np.ndarray, indices: np.ndarray) -> None:
+    """output.bin in the layout of kmer_searcher.cpp:98-130 (input order, ascending indices)."""
+    L = _lib.lib()
+    enc = [n.encode() for n in names]
+    noff = np.zeros(len(enc) + 1, dtype=np.int64)
+    np.cumsum([len(e) for e in enc], out=noff[1:])
+    blob = b"".join(enc) or b"\0"
+    indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    if indices.size == 0:
+        indices = np.zeros(1, dtype=np.int32)
+    rc = L.fr_write_output_bin(path.encode(), C.c_char_p(blob), noff.ctypes.data_as(C.c_void_p), len(enc),
+                               indptr.ctypes.data_as(C.c_void_p), indices.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise FedrannError("ID contains non-ASCII characters" if rc == -2 else f"fr_write_output_bin: {rc}")
+
+
+def write_frequency_bin(path: str, docfreq: np.ndarray) -> None:
+    L = _lib.lib()
+    docfreq = np.ascontiguousarray(docfreq, dtype=np.uint32)
+    check(None, L.fr_write_frequency_bin(path.encode(), docfreq.ctypes.data_as(C.c_void_p), len(docfreq)),
+          "fr_write_frequency_bin")
+
+
+# ---------------------------------------------------------------------------
+class Engine:
+    def __init__(self, device: int | None = None):
+        if not torch.cuda.is_available():
+            raise FedrannError("fedrann_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.L = _lib.lib()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        torch.cuda.set_device(self.device)
+        h = C.c_void_p()
+        rc = self.L.fr_create(self.device, C.byref(h))
+        if rc != 0:
+            raise FedrannError(f"fr_create failed ({rc}): an sm_100 GPU is required")
+        self.h = h
+        self.k = None
+        self.n_features = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.fr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self) -> int:
+        return int(self.L.fr_launch_count(self.h))
+
+    def dev(self, a: np.ndarray, dtype=None) -> torch.Tensor:
+        t = torch.from_numpy(np.ascontiguousarray(a))
+        if dtype is not None:
+            t = t.to(dtype)
+        return t.to(f"cuda:{self.device}", non_blocking=True)
+
+    # -- K2 --------------------------------------------------------------
+    def build_table(self, codes, k: int) -> None:
+        """codes: uint64 numpy (or int64-viewed cuda tensor), feature index -> k-mer code."""
+        if isinstance(codes, np.ndarray):
+            codes = self.dev(np.ascontiguousarray(codes, dtype=np.uint64).view(np.int64))
+        self._codes = codes
+        check(self.h, self.L.fr_table_build(self.h, _ptr(codes), codes.numel(), k, _stream()), "fr_table_build")
+        self.k = k
+        self.n_features = codes.numel()
+
+    # -- K1 + K3 ---------------------------------------------------------
+    def extract(self, bases: torch.Tensor, offsets: torch.Tensor, docfreq: torch.Tensor | None = None):
+        """-> (indptr int64[R+1], indices int32[nnz]) on the device; CSR rows in
+        input order, columns ascending.  docfreq (int32/uint32 [F]) is added to."""
+        assert bases.dtype == torch.uint8 and offsets.dtype == torch.int64
+        R = offsets.numel() - 1
+        indptr = torch.empty(R + 1, dtype=torch.int64, device=bases.device)
+        nnz = C.c_int64(0)
+        check(self.h, self.L.fr_extract_count(self.h, _ptr(bases), bases.numel(), _ptr(offsets), R, _ptr(indptr),
+                                              _ptr(docfreq), C.byref(nnz), _stream()), "fr_extract_count")
+        indices = torch.empty(max(nnz.value, 1), dtype=torch.int32, device=bases.device)
+        check(self.h, self.L.fr_extract_fill(self.h, _ptr(indices), _stream()), "fr_extract_fill")
+        return indptr, indices[: nnz.value]
+
+    # -- K4 --------------------------------------------------------------
+    def upload_projection(self, P_csr):
+        """scipy CSR (F x D) fp32 -> device triple."""
+        P_csr = P_csr.tocsr()
+        return (self.dev(P_csr.indptr.astype(np.int64)), self.dev(P_csr.indices.astype(np.int32)),
+                self.dev(P_csr.data.astype(np.float32)), int(P_csr.shape[1]))
+
+    def project(self, indptr, indices, P_dev, nk: int, out: torch.Tensor | None = None) -> torch.Tensor:
+        p_indptr, p_indices, p_data, D = P_dev
+        R = indptr.numel() - 1
+        E = out if out is not None else torch.empty((2 * R, D), dtype=torch.float32, device=indptr.device)
+        if indices.numel() == 0:
+            indices = torch.zeros(1, dtype=torch.int32, device=indptr.device)
+        if p_indices.numel() == 0:
+            p_indices = torch.zeros(1, dtype=torch.int32, device=indptr.device)
+            p_data = torch.zeros(1, dtype=torch.float32, device=indptr.device)
+        check(self.h, self.L.fr_project(self.h, _ptr(indptr), _ptr(indices), R, _ptr(p_indptr), _ptr(p_indices),
+                                        _ptr(p_data), nk, D, _ptr(E), _stream()), "fr_project")
+        return E
+
+    # -- K5 --------------------------------------------------------------
+    def normalize(self, E: torch.Tensor):
+        N, D = E.shape
+        Dp = (D + 63) // 64 * 64
+        En = torch.empty_like(E)
+        Eh = torch.empty((N, Dp), dtype=torch.float16, device=E.device)
+        norms = torch.empty(N, dtype=torch.float32, device=E.device)
+        check(self.h, self.L.fr_normalize(self.h, _ptr(E), N, D, Dp, _ptr(En), _ptr(Eh), _ptr(norms), _stream()),
+              "fr_normalize")
+        return En, Eh, norms
+
+    # -- K6 + K7 ---------------------------------------------------------
+    def knn(self, En, Eh, norms, k: int, q0: int = 0, nq: int | None = None, mode: int = 0):
+        N, D = En.shape
+        nq = N - q0 if nq is None else nq
+        idx = torch.empty((nq, k), dtype=torch.int32, device=En.device)
+        dist = torch.empty((nq, k), dtype=torch.float32, device=En.device)
+        Dp = Eh.shape[1] if Eh is not None else D
+        check(self.h, self.L.fr_knn(self.h, _ptr(En), _ptr(Eh), _ptr(norms), N, D, Dp, q0, nq, k, mode,
+                                    _ptr(idx), _ptr(dist), _stream()), "fr_knn")
+        return idx, dist
+
+    @property
+    def knn_fallback_rows(self) -> int:
+        return int(self.L.fr_knn_last_fallback_rows(self.h))

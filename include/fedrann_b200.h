@@ -1,0 +1,110 @@
+/*
+ * fedrann_b200.h -- C ABI of the B200-native FEDRANN hot path
+ * (k-mer feature extraction -> sparse random projection -> exact cosine kNN).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch / C++ types.
+ * One fr_ctx per GPU (per rank).  Device pointers are caller-owned (e.g.
+ * torch.Tensor.data_ptr()); `stream` is a cudaStream_t passed as void*.
+ * Every function returns FR_OK (0) or a negative FR_ERR_* code; the message of
+ * the last error on a context is available through fr_last_error().  No C++
+ * exception crosses this boundary.  Unless stated otherwise calls are
+ * asynchronous on `stream`.
+ *
+ * Reference interfaces replaced (paths relative to the FEDRANN repository):
+ *   kmer_searcher/kmer_searcher.cpp:232-375   the kmer_searcher executable
+ *   fedrann/feature_extraction.py:167-292     get_feature_matrix (A_chunk.dot(P))
+ *   fedrann/nearest_neighbors.py:22-55        NNDescent_ava.get_neighbors
+ */
+#ifndef FEDRANN_B200_H
+#define FEDRANN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FR_OK 0
+#define FR_ERR_CUDA (-1)      /* a CUDA runtime call failed                   */
+#define FR_ERR_ARG (-2)       /* invalid argument                              */
+#define FR_ERR_STATE (-3)     /* call order violated (e.g. fill before count)  */
+#define FR_ERR_NOMEM (-4)     /* device allocation failed                      */
+#define FR_ERR_NO_DEVICE (-5) /* no usable sm_100 device                       */
+
+typedef struct fr_ctx fr_ctx;
+
+int fr_version(void);
+int fr_create(int device, fr_ctx **out);
+void fr_destroy(fr_ctx *ctx);
+const char *fr_last_error(const fr_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py: gpu_launches) */
+int64_t fr_launch_count(const fr_ctx *ctx);
+
+/* ---- host-side parsers (native equivalents of the reference's C++ I/O) ---- */
+
+/* kmer_searcher.cpp:259-273.  Whitespace-separated tokens; wrong-length,
+ * non-ACGT and duplicate tokens are skipped and consume no index.  Writes
+ * index -> 2-bit code (A0 C1 G2 T3, first base most significant) to
+ * codes_out (capacity cap); *n_out = number of unique k-mers (may exceed cap:
+ * call again with a larger buffer). */
+int fr_library_parse(const char *text, int64_t text_len, int k, uint64_t *codes_out,
+                     int64_t cap, int64_t *n_out);
+
+/* kmer_searcher.cpp:153-201.  FASTA/FASTQ text -> concatenated bases +
+ * offsets + names.  Two-call protocol: with bases_out == NULL only the counts
+ * are returned.  names_out receives the names separated by '\n'. */
+int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64_t *offsets_out,
+                   char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len);
+
+/* kmer_searcher.cpp:98-130 and 203-229: output.bin / kmer_frequency.bin
+ * writers (rows in input order, indices ascending). */
+int fr_write_output_bin(const char *path, const char *names, const int64_t *name_offsets,
+                        int64_t n_reads, const int64_t *indptr, const int32_t *indices);
+int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features);
+
+/* ---- K2: k-mer library -> device lookup table (kmer_searcher.cpp:259-273) ---- */
+/* d_codes: device u64[n], feature index -> k-mer code, all distinct. */
+int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, int k, void *stream);
+
+/* ---- K1+K3: reads -> CSR feature matrix (kmer_searcher.cpp:295-354) ---- */
+/* d_bases: device u8 ASCII, 16-byte aligned, all reads concatenated;
+ * d_offsets: device i64[n_reads+1].  Fills d_indptr (i64[n_reads+1]) and, when
+ * non-NULL, ADDS per-feature document frequencies into d_docfreq (u32[F]).
+ * Synchronises `stream` and returns the number of non-zeros in *nnz_out. */
+int fr_extract_count(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,
+                     int64_t n_reads, int64_t *d_indptr, uint32_t *d_docfreq, int64_t *nnz_out,
+                     void *stream);
+/* Writes the column indices (i32[nnz], ascending inside each row, rows in
+ * input order) of the preceding fr_extract_count. */
+int fr_extract_fill(fr_ctx *ctx, int32_t *d_indices, void *stream);
+
+/* ---- K4: E = A.P (feature_extraction.py:204-213, 136-140) ---- */
+/* P in CSR (F = 2*nk rows, D columns): d_p_indptr i64[F+1], d_p_indices
+ * i32[nnzP], d_p_data f32[nnzP].  d_E: f32[2*n_reads, D]; row 2r = forward,
+ * row 2r+1 = index-swapped reverse orientation.  Accumulation is sequential
+ * fp32 in ascending feature order (bit-exact with scipy's csr_matmat). */
+int fr_project(fr_ctx *ctx, const int64_t *d_indptr, const int32_t *d_indices, int64_t n_reads,
+               const int64_t *d_p_indptr, const int32_t *d_p_indices, const float *d_p_data,
+               int64_t nk, int D, float *d_E, void *stream);
+
+/* ---- K5: row normalisation for cosine kNN ---- */
+/* d_En: f32[N, D] unit rows (zero rows stay zero); d_Eh: f16[N, Dp] copy
+ * padded with zeros to Dp (multiple of 64, >= D); d_norms: f32[N]. */
+int fr_normalize(fr_ctx *ctx, const float *d_E, int64_t N, int D, int Dp, float *d_En, void *d_Eh,
+                 float *d_norms, void *stream);
+
+/* ---- K6+K7: exact cosine kNN (nearest_neighbors.py:22-55) ---- */
+/* Queries = database rows [q0, q0+nq); database = all n_db rows.  Output
+ * d_idx i32[nq,k], d_dist f32[nq,k], ascending distance, ties by lower index.
+ * mode 0 = tensor-core candidate pass + fp32 re-rank with certification
+ * (uncertified rows fall back to the exact scan); mode 1 = exact fp32 scan. */
+int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db,
+           int D, int Dp, int64_t q0, int64_t nq, int k, int mode, int32_t *d_idx, float *d_dist,
+           void *stream);
+/* statistics of the last fr_knn call: rows that needed the exact fallback */
+int64_t fr_knn_last_fallback_rows(const fr_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,96 @@
+"""CPU-side checks of the C ABI: the library loads, exports every symbol the
+header declares, and its host-side parsers/writers agree with the oracle and
+the reference goldens (no GPU compute here)."""
+import ctypes as C
+import os
+import re
+from os.path import abspath, dirname, join
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from helpers import EXTRACT_CASES, load_extract_golden, reads_to_arrays
+
+ROOT = dirname(dirname(abspath(__file__)))
+
+
+def _declared():
+    hdr = open(join(ROOT, "include", "fedrann_b200.h")).read()
+    return sorted(set(re.findall(r"\b(fr_[a-z0-9_]+)\s*\(", hdr)) - {"fr_ctx"})
+
+
+def test_library_exports_every_declared_symbol():
+    from fedrann_b200 import _lib
+    L = C.CDLL(_lib.LIB_PATH)
+    names = _declared()
+    assert len(names) >= 16
+    for n in names:
+        assert hasattr(L, n), n
+    assert sorted(_lib.SYMBOLS) == names
+    assert L.fr_version() >= 100
+
+
+def test_no_device_is_an_error_not_a_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from fedrann_b200 import engine
+    with pytest.raises(Exception):
+        engine.Engine()
+
+
+def test_product_never_imports_oracle():
+    pkg = join(ROOT, "fedrann_b200")
+    pat = re.compile(r"^\s*(from|import)\s+oracle|liboracle|orc_", re.M)
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                assert not pat.search(open(join(dp, f)).read()), join(dp, f)
+
+
+@pytest.mark.parametrize("tag", EXTRACT_CASES)
+def test_host_parsers_match_oracle(tag):
+    from fedrann_b200 import engine
+    g = load_extract_golden(tag)
+    codes = engine.parse_library(g["lib_text"], g["k"])
+    lib = O.Library(g["lib_text"], g["k"])
+    assert np.array_equal(codes, lib.codes)
+    bases, offs, names = engine.parse_fastx(g["fastx_text"])
+    recs = O.parse_fastx(g["fastx_text"])
+    b2, o2, n2 = reads_to_arrays(recs)
+    assert names == n2
+    assert np.array_equal(offs, o2)
+    assert bases.tobytes() == b2.tobytes()
+    assert sorted(names) == sorted(g["names"])
+
+
+def test_fastx_edge_cases():
+    from fedrann_b200 import engine
+    cases = [
+        b"", b"\n\n", b">a\n", b">\nACGT\n>b x\nAC\n\nGT\n", b"ACGT\n>a\nAC", b">a\tz\nAC\r\nGT\n",
+        b"@q1 d\nACGT\n+\n!!!!\n@q2\nAC\n+\n!!\n", b"@q1\nACGT", b"@\nAC\n+\n!!\n", b"\n@q\nAC\n+\n!!\n",
+    ]
+    for text in cases:
+        bases, offs, names = engine.parse_fastx(text)
+        recs = O.parse_fastx(text)
+        b2, o2, n2 = reads_to_arrays(recs)
+        assert names == n2, text
+        assert np.array_equal(offs, o2), text
+        assert bases.tobytes() == b2.tobytes(), text
+
+
+def test_output_bin_roundtrip(tmp_path):
+    from fedrann_b200 import engine
+    names = ["r1", "read two", "z"]
+    indptr = np.array([0, 2, 2, 5], dtype=np.int64)
+    indices = np.array([3, 9, 0, 4, 2**31 - 1], dtype=np.int32)
+    p = str(tmp_path / "output.bin")
+    engine.write_output_bin(p, names, indptr, indices)
+    recs = O.read_output_bin(p)
+    assert recs == [("r1", [3, 9]), ("read two", []), ("z", [0, 4, 2**31 - 1])]
+    with pytest.raises(Exception):
+        engine.write_output_bin(p, ["bad\x01"], np.array([0, 0]), np.zeros(0, np.int32))
+    f = str(tmp_path / "kmer_frequency.bin")
+    engine.write_frequency_bin(f, np.array([0, 2, 0, 7], dtype=np.uint32))
+    assert O.read_frequency_bin(f) == {1: 2, 3: 7}

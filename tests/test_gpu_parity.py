@@ -1,0 +1,207 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle and the
+reference goldens.  Integer / index work is bit-exact; the projection is
+bit-exact (same fp32 accumulation order as scipy); kNN distances agree within
+1e-5 (fp32 dot-product summation order) and indices agree except where two
+neighbours are closer than that tolerance."""
+from os.path import join
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+from fedrann_b200 import synthetic as S
+from helpers import GOLDEN, EXTRACT_CASES, load_extract_golden, reads_to_arrays, csr_rows
+
+pytestmark = pytest.mark.gpu
+
+KNN_ATOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from fedrann_b200.engine import Engine
+    e = Engine(0)
+    yield e
+    e.close()
+
+
+def gpu_extract(eng, codes, k, bases, offs, with_freq=True):
+    eng.build_table(codes, k)
+    b = eng.dev(bases) if len(bases) else torch.zeros(16, dtype=torch.uint8, device="cuda")[:0]
+    o = eng.dev(offs)
+    df = torch.zeros(max(len(codes), 1), dtype=torch.int32, device="cuda") if with_freq else None
+    indptr, indices = eng.extract(b, o, df)
+    torch.cuda.synchronize()
+    return indptr.cpu().numpy(), indices.cpu().numpy(), (df.cpu().numpy()[: len(codes)] if with_freq else None)
+
+
+@pytest.mark.parametrize("tag", EXTRACT_CASES)
+def test_extract_golden_bit_exact(eng, tag):
+    from fedrann_b200 import engine
+    g = load_extract_golden(tag)
+    codes = engine.parse_library(g["lib_text"], g["k"])
+    bases, offs, names = engine.parse_fastx(g["fastx_text"])
+    indptr, indices, df = gpu_extract(eng, codes, g["k"], bases, offs)
+    assert csr_rows(indptr, indices, names) == g["rows"]
+    assert {i: int(c) for i, c in enumerate(df) if c} == g["freq"]
+
+
+def _check_vs_oracle(eng, lib_text, k, bases, offs):
+    from fedrann_b200 import engine
+    codes = engine.parse_library(lib_text, k)
+    L = O.Library(lib_text, k)
+    ip, ix, df = O.extract(L, bases, offs)
+    indptr, indices, gdf = gpu_extract(eng, codes, k, bases, offs)
+    assert np.array_equal(indptr, ip)
+    assert np.array_equal(indices, ix)
+    assert np.array_equal(gdf.astype(np.uint64), df)
+    return indptr, indices
+
+
+@pytest.mark.parametrize("k", [1, 2, 5, 13, 16, 21, 31])
+def test_extract_random_reads_all_k(eng, k):
+    g = S.random_genome(20000, 100 + k)
+    rs = S.simulate_reads(g, 6, k, mean_len=2500, len_model="lognormal", min_len=1, sub=0.03, ins=0.01,
+                          dele=0.01, n_frac=0.004)
+    frac = 1.0 if k < 8 else 0.2
+    lib = S.library_from_reads(rs, k, frac, 1, 9)
+    _check_vs_oracle(eng, lib.searcher_text(), k, rs.bases, rs.offsets)
+
+
+def test_extract_ragged_and_empty(eng):
+    k = 7
+    lib_text = b"AAAAAAA\nACGTACG\nCGTACGT\nTTTTTTT\nGTACGTA\n"
+    seqs = [b"", b"A", b"ACGTACGTACGT", b"", b"NNNNNNNN", b"acgtacgNacgtacgt", b"TTTTTTTTTTTTTTTTTTT", b"ACG", b""]
+    bases = np.frombuffer(b"".join(seqs), dtype=np.uint8)
+    offs = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int64)
+    _check_vs_oracle(eng, lib_text, k, bases, offs)
+    # no reads at all
+    _check_vs_oracle(eng, lib_text, k, np.zeros(0, np.uint8), np.zeros(1, np.int64))
+    # empty library
+    _check_vs_oracle(eng, b"", k, bases, offs)
+
+
+def test_extract_long_reads_multi_tile_and_spill(eng):
+    # every k-mer of the genome is in the library: a 40 kb read carries ~40k distinct
+    # hits, far beyond the shared-memory hit list -> exercises compaction + global spill
+    k = 15
+    g = S.random_genome(50000, 77)
+    rs = S.simulate_reads(g, 8, 3, mean_len=40000, len_model="fixed", sub=0.001)
+    lib = S.library_from_genome(g, k, 1.0, 8, 5)
+    ip, ix = _check_vs_oracle(eng, lib.searcher_text(), k, rs.bases, rs.offsets)
+    assert np.diff(ip).max() > 8192
+    # a read of one repeated unit: thousands of duplicate hits, few distinct
+    rep = np.frombuffer(b"ACGGTCATTGCAGGCTTAACG" * 3000, dtype=np.uint8)
+    _check_vs_oracle(eng, lib.searcher_text() + b"ACGGTCATTGCAGGC\nCGGTCATTGCAGGCT\n", k, rep,
+                     np.array([0, len(rep)], dtype=np.int64))
+
+
+def test_extract_properties_at_scale(eng):
+    k = 15
+    g = S.random_genome(1_000_000, 1)
+    rs = S.simulate_reads(g, 20, 2, mean_len=10000, len_model="lognormal", min_len=1000, sub=0.02, ins=0.02,
+                          dele=0.02)
+    lib = S.library_from_genome(g, k, 0.05, 20, 602)
+    codes = lib.all_codes()
+    indptr, indices, df = gpu_extract(eng, codes, k, rs.bases, rs.offsets)
+    assert indptr[0] == 0 and np.all(np.diff(indptr) >= 0) and indptr[-1] == len(indices)
+    rows = np.repeat(np.arange(rs.n_reads), np.diff(indptr))
+    d = np.diff(indices.astype(np.int64))
+    same = rows[1:] == rows[:-1]
+    assert np.all(d[same] > 0)                       # strictly ascending inside every row
+    assert indices.min() >= 0 and indices.max() < len(codes)
+    assert int(df.sum()) == len(indices)             # checksum of checksums
+    assert np.array_equal(np.bincount(indices, minlength=len(codes)), df)
+    # idempotence
+    i2, x2, _ = gpu_extract(eng, codes, k, rs.bases, rs.offsets)
+    assert np.array_equal(i2, indptr) and np.array_equal(x2, indices)
+    # a seeded sample of rows against the oracle
+    L = O.Library(lib.searcher_text(), k)
+    sel = np.random.default_rng(0).choice(rs.n_reads, 40, replace=False)
+    for r in sel:
+        b = rs.bases[rs.offsets[r]:rs.offsets[r + 1]]
+        ip, ix, _ = O.extract(L, b, np.array([0, len(b)], dtype=np.int64))
+        assert np.array_equal(indices[indptr[r]:indptr[r + 1]], ix)
+
+
+def test_project_bit_exact_vs_golden_and_oracle(eng):
+    from fedrann_b200 import engine
+    z = np.load(join(GOLDEN, "project_s0.npz"))
+    g = load_extract_golden("s0")
+    codes = engine.parse_library(g["lib_text"], g["k"])
+    bases, offs, names = engine.parse_fastx(g["fastx_text"])
+    eng.build_table(codes, g["k"])
+    indptr, indices = eng.extract(eng.dev(bases), eng.dev(offs))
+    D, F = int(z["D"]), int(z["n_features"])
+    P = O.precompute_matrix(D, z["counts"], F)
+    E = eng.project(indptr, indices, eng.upload_projection(P), F // 2).cpu().numpy()
+    E_or = O.project(indptr.cpu().numpy(), indices.cpu().numpy(), P, F // 2)
+    assert np.array_equal(E.view(np.uint32), E_or.view(np.uint32))
+    pos = {n: i for i, n in enumerate(names)}
+    for row, (n, s) in enumerate(zip([str(x) for x in z["names"]], z["strands"])):
+        assert np.array_equal(E[2 * pos[n] + int(s)].view(np.uint32), z["E_ref"][row].view(np.uint32))
+
+
+@pytest.mark.parametrize("D", [1, 33, 256, 500])
+def test_project_dense_rows_and_empty_rows(eng, D):
+    import scipy.sparse as sp
+    rng = np.random.default_rng(D)
+    nk, R = 300, 50
+    F = 2 * nk
+    # a dense-ish P forces same-column collisions inside one staged group and the sequential path
+    dens = 0.9 if D <= 33 else 0.05
+    P = sp.random(F, D, density=dens, format="csr", dtype=np.float32, random_state=3)
+    P.data = (rng.standard_normal(len(P.data)) * 3).astype(np.float32)
+    rows = [np.sort(rng.choice(F, rng.integers(0, 120), replace=False)) for _ in range(R)]
+    rows[3] = np.zeros(0, dtype=np.int64)
+    indptr = np.concatenate([[0], np.cumsum([len(r) for r in rows])]).astype(np.int64)
+    indices = np.concatenate(rows).astype(np.int32)
+    E = eng.project(eng.dev(indptr), eng.dev(indices), eng.upload_projection(P), nk).cpu().numpy()
+    E_or = O.project(indptr, indices, P, nk)
+    assert np.array_equal(E.view(np.uint32), E_or.view(np.uint32))
+    assert not E[6].any() and not E[7].any()
+
+
+def _knn_agree(idx, dist, oidx, odist):
+    assert np.allclose(dist, odist, atol=KNN_ATOL, rtol=0)
+    bad = idx != oidx
+    if bad.any():
+        # a mismatch is only legitimate between near-ties
+        r, c = np.nonzero(bad)
+        for i, j in zip(r, c):
+            near = np.abs(odist[i] - odist[i, j]) <= 2 * KNN_ATOL
+            assert idx[i, j] in oidx[i][near], (i, j)
+    return 1.0 - bad.mean()
+
+
+@pytest.mark.parametrize("mode", [1, 0])
+@pytest.mark.parametrize("N,D,k", [(700, 48, 10), (1500, 500, 50), (300, 64, 20), (130, 256, 128)])
+def test_knn_vs_oracle(eng, mode, N, D, k):
+    rng = np.random.default_rng(N + D)
+    X = rng.standard_normal((N, D)).astype(np.float32)
+    X[rng.random((N, D)) < 0.5] = 0       # projected embeddings are half zeros
+    X[5] = 0                              # zero-norm row
+    X[11] = X[10]                         # exact duplicate rows -> ties
+    En, Eh, norms = eng.normalize(eng.dev(X))
+    idx, dist = eng.knn(En, Eh, norms, k, mode=mode)
+    torch.cuda.synchronize()
+    oidx, odist = O.knn(X, k)
+    agree = _knn_agree(idx.cpu().numpy(), dist.cpu().numpy(), oidx, odist)
+    assert agree > 0.99
+    # query slice (what one rank of the sharded search does)
+    q0, nq = N // 3, N // 4
+    i2, d2 = eng.knn(En, Eh, norms, k, q0=q0, nq=nq, mode=mode)
+    assert torch.equal(i2, idx[q0:q0 + nq]) and torch.equal(d2, dist[q0:q0 + nq])
+
+
+def test_normalize_matches_oracle(eng):
+    rng = np.random.default_rng(4)
+    X = rng.standard_normal((257, 100)).astype(np.float32)
+    X[9] = 0
+    En, Eh, norms = eng.normalize(eng.dev(X))
+    Xn, on = O.normalize(X)
+    assert np.allclose(En.cpu().numpy(), Xn, atol=3e-7)
+    assert np.allclose(norms.cpu().numpy(), on, rtol=1e-6)
+    assert Eh.shape == (257, 128) and not Eh[:, 100:].any()
+    assert np.allclose(Eh[:, :100].float().cpu().numpy(), Xn, atol=1e-3)

@@ -1,0 +1,78 @@
+"""Host-side logic that runs without a GPU: the projection operand, read
+sharding, and the world_size-2 gloo path of the all-gather."""
+import os
+import sys
+from os.path import abspath, dirname, join
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from helpers import GOLDEN
+
+ROOT = dirname(dirname(abspath(__file__)))
+
+
+def test_precompute_matches_oracle_and_reference_structure():
+    from fedrann_b200.precompute import precompute_matrix
+    z = np.load(join(GOLDEN, "project_s0.npz"))
+    A = precompute_matrix(int(z["D"]), z["counts"], int(z["n_features"]))
+    B = O.precompute_matrix(int(z["D"]), z["counts"], int(z["n_features"]))
+    assert np.array_equal(A.indptr, B.indptr) and np.array_equal(A.indices, B.indices)
+    assert np.array_equal(A.data.view(np.uint32), B.data.view(np.uint32))
+    assert np.array_equal(A.indptr.astype(np.int64), z["P_ref_indptr"])
+    assert np.array_equal(A.indices.astype(np.int32), z["P_ref_indices"])
+
+
+def test_get_precompute_matrix_reads_counter_file(tmp_path):
+    from fedrann_b200.precompute import get_precompute_matrix, kmer_count_generator
+    p = tmp_path / "fwd_kmer_library.fasta"
+    p.write_text(">3\nACGTA\n>7\nCCGTA\n>2\nTTGTA\n")
+    assert list(kmer_count_generator(str(p), 3)) == [(0, 3), (3, 3), (1, 7), (4, 7), (2, 2), (5, 2)]
+    P, nf = get_precompute_matrix(8, str(p), 6)
+    assert nf == 6 and P.shape == (6, 8) and P.dtype == np.float32
+
+
+def test_shard_reads_balanced_and_contiguous():
+    from fedrann_b200.parallel import shard_reads
+    rng = np.random.default_rng(0)
+    lens = rng.integers(1, 20000, 1000)
+    offs = np.concatenate([[0], np.cumsum(lens)])
+    for w in (1, 2, 4, 8):
+        b = shard_reads(offs, w)
+        assert b[0] == 0 and b[-1] == 1000 and np.all(np.diff(b) >= 0)
+        sizes = [offs[b[r + 1]] - offs[b[r]] for r in range(w)]
+        assert max(sizes) - min(sizes) <= 2 * lens.max()
+    assert list(shard_reads(np.array([0]), 4)) == [0, 0, 0, 0, 0]
+
+
+def _gloo_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from fedrann_b200.parallel import init_from_env, all_gather_rows
+    init_from_env("gloo")
+    n = 5 + 3 * rank
+    En = torch.full((n, 4), float(rank)) + torch.arange(n)[:, None]
+    Eh = En.to(torch.float16)
+    norms = torch.arange(n, dtype=torch.float32) + 100 * rank
+    A, B, C, q0 = all_gather_rows(En, Eh, norms)
+    q.put((rank, A.tolist(), C.tolist(), q0))
+    dist.destroy_process_group()
+
+
+def test_all_gather_rows_world2_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    ps = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    [p.join(60) for p in ps]
+    (r0, A0, C0, q00), (r1, A1, C1, q01) = res
+    assert A0 == A1 and C0 == C1 and len(A0) == 13
+    assert q00 == 0 and q01 == 5
+    assert C0[:5] == [0, 1, 2, 3, 4] and C0[5:] == [100 + i for i in range(8)]
