@@ -17,6 +17,7 @@ _ERR = {-1: "FR_ERR_CUDA", -2: "FR_ERR_ARG", -3: "FR_ERR_STATE", -4: "FR_ERR_NOM
 
 SYMBOLS = [
     "fr_version", "fr_create", "fr_destroy", "fr_last_error", "fr_launch_count",
+    "fr_profile_enable", "fr_profile_read",
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
     "fr_table_build", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_last_fallback_rows",
@@ -58,6 +59,8 @@ def lib():
     L.fr_last_error.restype = C.c_char_p
     L.fr_launch_count.argtypes = [vp]
     L.fr_launch_count.restype = i64
+    L.fr_profile_enable.argtypes = [vp, i32]
+    L.fr_profile_read.argtypes = [vp, C.c_char_p, i64, C.POINTER(i64)]
     L.fr_library_parse.argtypes = [C.c_char_p, i64, i32, vp, i64, C.POINTER(i64)]
     L.fr_fastx_parse.argtypes = [C.c_char_p, i64, vp, vp, vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     L.fr_write_output_bin.argtypes = [C.c_char_p, vp, vp, i64, vp, vp]

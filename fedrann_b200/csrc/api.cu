@@ -2,6 +2,7 @@
 #include "common.cuh"
 
 #include <cstdio>
+#include <cstring>
 #include <new>
 
 int fr_fail(fr_ctx *ctx, int code, const char *what) {
@@ -24,6 +25,67 @@ int fr_ensure(fr_ctx *ctx, void **ptr, int64_t *cap, int64_t need_bytes, const c
     cudaError_t e = cudaMalloc(ptr, (size_t)need_bytes);
     if (e != cudaSuccess) { *ptr = nullptr; return fr_cuda_fail(ctx, e, what); }
     *cap = need_bytes;
+    return FR_OK;
+}
+
+// ---- per-kernel timing: one event pair around every launch while enabled ----
+void fr_kt_begin(fr_ctx *ctx, const char *name, cudaStream_t st) {
+    if (!ctx->kt_on) return;
+    fr_ctx::KtRec r;
+    r.name = name;
+    if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return;
+    cudaEventRecord(r.e0, st);
+    ctx->kt.push_back(r);
+    ctx->kt_stream = st;
+    ctx->kt_open = true;
+}
+
+void fr_kt_end(fr_ctx *ctx) {
+    cudaEventRecord(ctx->kt.back().e1, ctx->kt_stream);
+    ctx->kt_open = false;
+}
+
+static void fr_kt_clear(fr_ctx *ctx) {
+    for (auto &r : ctx->kt) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+    ctx->kt.clear();
+    ctx->kt_open = false;
+}
+
+extern "C" int fr_profile_enable(fr_ctx *ctx, int on) {
+    if (!ctx) return FR_ERR_ARG;
+    fr_kt_clear(ctx);
+    ctx->kt_on = on != 0;
+    return FR_OK;
+}
+
+extern "C" int fr_profile_read(fr_ctx *ctx, char *buf, int64_t cap, int64_t *len_out) {
+    if (!ctx || !len_out) return FR_ERR_ARG;
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    struct Agg { const char *name; int64_t n; double ms; };
+    std::vector<Agg> agg;
+    for (auto &r : ctx->kt) {
+        FR_CUDA(ctx, cudaEventSynchronize(r.e1));
+        float ms = 0.f;
+        FR_CUDA(ctx, cudaEventElapsedTime(&ms, r.e0, r.e1));
+        size_t i = 0;
+        for (; i < agg.size(); ++i) if (std::string(agg[i].name) == r.name) break;
+        if (i == agg.size()) agg.push_back({r.name, 0, 0.0});
+        agg[i].n++;
+        agg[i].ms += ms;
+    }
+    std::string out;
+    char line[256];
+    for (auto &a : agg) {
+        snprintf(line, sizeof line, "%s %lld %.6f\n", a.name, (long long)a.n, a.ms);
+        out += line;
+    }
+    *len_out = (int64_t)out.size();
+    if (buf && cap > 0) {
+        size_t n = out.size() < (size_t)cap - 1 ? out.size() : (size_t)cap - 1;
+        memcpy(buf, out.data(), n);
+        buf[n] = 0;
+    }
+    fr_kt_clear(ctx);
     return FR_OK;
 }
 
@@ -60,6 +122,7 @@ extern "C" void fr_destroy(fr_ctx *ctx) {
     cudaFree(ctx->d_read_cnt); cudaFree(ctx->d_counters); cudaFree(ctx->d_scan_tmp);
     cudaFree(ctx->d_knn_ws);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    fr_kt_clear(ctx);
     delete ctx;
 }
 

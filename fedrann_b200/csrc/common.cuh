@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include <string>
+#include <vector>
 
 #include "../../include/fedrann_b200.h"
 
@@ -54,6 +55,13 @@ struct fr_ctx {
     int64_t last_n_reads = -1;
     const int64_t *last_indptr = nullptr;
 
+    // per-kernel CUDA-event timing (fr_profile_enable / fr_profile_read)
+    struct KtRec { const char *name; cudaEvent_t e0, e1; };
+    bool kt_on = false;
+    bool kt_open = false;
+    cudaStream_t kt_stream = nullptr;
+    std::vector<KtRec> kt;
+
     // K6/K7 scratch
     void *d_knn_ws = nullptr;
     int64_t knn_ws_cap = 0;
@@ -70,9 +78,13 @@ int fr_ensure(fr_ctx *ctx, void **ptr, int64_t *cap, int64_t need_bytes, const c
         if (_e != cudaSuccess) return fr_cuda_fail(ctx, _e, #call); \
     } while (0)
 
+void fr_kt_begin(fr_ctx *ctx, const char *name, cudaStream_t st);
+void fr_kt_end(fr_ctx *ctx);
+
 #define FR_LAUNCH_CHECK(ctx, name)                               \
     do {                                                         \
         (ctx)->launches++;                                       \
+        if ((ctx)->kt_open) fr_kt_end(ctx);                      \
         cudaError_t _e = cudaGetLastError();                     \
         if (_e != cudaSuccess) return fr_cuda_fail(ctx, _e, name); \
     } while (0)

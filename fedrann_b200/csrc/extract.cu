@@ -356,6 +356,7 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
                                           (int)sizeof(FrExtractShared)));
         attr_set = true;
     }
+    fr_kt_begin(ctx, "fr_extract_kernel", st);
     fr_extract_kernel<<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
         d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
         ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters);
@@ -364,6 +365,7 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
 }
 
 int fr_scan_counts(fr_ctx *ctx, const int32_t *d_cnt, int64_t n, int64_t *d_indptr, cudaStream_t st) {
+    fr_kt_begin(ctx, "fr_scan_kernel", st);
     fr_scan_kernel<<<1, 1024, 0, st>>>(d_cnt, n, d_indptr);
     FR_LAUNCH_CHECK(ctx, "fr_scan_kernel");
     return FR_OK;
@@ -374,6 +376,7 @@ int fr_gather_rows(fr_ctx *ctx, int32_t *d_indices, cudaStream_t st) {
     if (n <= 0) return FR_OK;
     int64_t blocks = (n * 32 + 255) / 256;
     if (blocks > (int64_t)ctx->sm_count * 32) blocks = (int64_t)ctx->sm_count * 32;
+    fr_kt_begin(ctx, "fr_gather_kernel", st);
     fr_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(ctx->d_scratch, ctx->d_read_off, ctx->last_indptr, n,
                                                        d_indices);
     FR_LAUNCH_CHECK(ctx, "fr_gather_kernel");
@@ -384,6 +387,7 @@ int fr_docfreq_launch(fr_ctx *ctx, int64_t nnz, uint32_t *d_docfreq, cudaStream_
     if (nnz <= 0) return FR_OK;
     int64_t blocks = (nnz + 255) / 256;
     if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
+    fr_kt_begin(ctx, "fr_docfreq_kernel", st);
     fr_docfreq_kernel<<<(unsigned)blocks, 256, 0, st>>>(ctx->d_scratch, nnz, d_docfreq);
     FR_LAUNCH_CHECK(ctx, "fr_docfreq_kernel");
     return FR_OK;

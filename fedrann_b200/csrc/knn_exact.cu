@@ -39,6 +39,7 @@ extern "C" int fr_normalize(fr_ctx *ctx, const float *d_E, int64_t N, int D, int
     FR_CUDA(ctx, cudaSetDevice(ctx->device));
     int64_t blocks = (N * 32 + 255) / 256;
     if (blocks > (int64_t)ctx->sm_count * 32) blocks = (int64_t)ctx->sm_count * 32;
+    fr_kt_begin(ctx, "fr_normalize_kernel", (cudaStream_t)stream);
     fr_normalize_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_E, N, D, Dp, d_En, (__half *)d_Eh,
                                                                            d_norms);
     FR_LAUNCH_CHECK(ctx, "fr_normalize_kernel");
@@ -151,6 +152,7 @@ int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, in
     int64_t blocks = (groups + FR_EX_WARPS - 1) / FR_EX_WARPS;
     if (blocks > (int64_t)ctx->sm_count * 8) blocks = (int64_t)ctx->sm_count * 8;
     if (blocks < 1) blocks = 1;
+    fr_kt_begin(ctx, "fr_knn_exact_kernel", st);
     fr_knn_exact_kernel<<<(unsigned)blocks, FR_EX_WARPS * 32, smem, st>>>(d_En, d_norms, n_db, D, q0, nq, k, d_rows,
                                                                           d_n_rows, d_idx, d_dist);
     FR_LAUNCH_CHECK(ctx, "fr_knn_exact_kernel");

@@ -124,6 +124,7 @@ extern "C" int fr_project(fr_ctx *ctx, const int64_t *d_indptr, const int32_t *d
     size_t smem = (size_t)2 * D * sizeof(float) + 2 * FR_PJ_STAGE * (sizeof(int) + sizeof(float));
     FR_CUDA(ctx, cudaFuncSetAttribute(fr_project_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t grid = n_reads < (int64_t)ctx->sm_count * 32 ? n_reads : (int64_t)ctx->sm_count * 32;
+    fr_kt_begin(ctx, "fr_project_kernel", (cudaStream_t)stream);
     fr_project_kernel<<<(unsigned)grid, 64, smem, (cudaStream_t)stream>>>(
         d_indptr, d_indices, n_reads, d_p_indptr, d_p_indices, d_p_data, nk, D, d_E);
     FR_LAUNCH_CHECK(ctx, "fr_project_kernel");

@@ -57,6 +57,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     if (n > 0) {
         int threads = 256;
         int64_t blocks = (n + threads - 1) / threads;
+        fr_kt_begin(ctx, "fr_table_insert_kernel", st);
         fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_keys, ctx->d_vals,
                                                                       ctx->d_bloom, lg_cap, lg_words);
         FR_LAUNCH_CHECK(ctx, "fr_table_insert_kernel");

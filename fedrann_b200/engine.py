@@ -109,6 +109,21 @@ class Engine:
     def launches(self) -> int:
         return int(self.L.fr_launch_count(self.h))
 
+    def profile(self, on: bool) -> None:
+        """Bracket every kernel launch with a CUDA event pair (see kernel_times)."""
+        check(self.h, self.L.fr_profile_enable(self.h, 1 if on else 0), "fr_profile_enable")
+
+    def kernel_times(self) -> dict:
+        """{kernel: (launches, total_ms)} since profile(True); clears the records."""
+        buf = C.create_string_buffer(1 << 16)
+        n = C.c_int64(0)
+        check(self.h, self.L.fr_profile_read(self.h, buf, len(buf), C.byref(n)), "fr_profile_read")
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, cnt, ms = line.split()
+            out[name] = (int(cnt), float(ms))
+        return out
+
     def dev(self, a: np.ndarray, dtype=None) -> torch.Tensor:
         t = torch.from_numpy(np.ascontiguousarray(a))
         if dtype is not None:

@@ -76,3 +76,47 @@ def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev,
     idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode)
     t.stop()
     return HotPathResult(indptr, indices, E, idx, dist, q0)
+
+
+@dataclass
+class HostBuffers:
+    """Pinned host memory either side of the path: the reads going in and the
+    neighbour lists coming out (what the CLI hands to / gets from the engine)."""
+    bases: torch.Tensor        # uint8 pinned
+    offsets: torch.Tensor      # int64 pinned [R+1]
+    nbr_idx: torch.Tensor      # int32 pinned (2R, k)
+    nbr_dist: torch.Tensor     # fp32 pinned (2R, k)
+
+    @classmethod
+    def from_device(cls, bases_d: torch.Tensor, offsets_np, n_rows: int, k: int) -> "HostBuffers":
+        b = torch.empty(bases_d.numel(), dtype=torch.uint8, pin_memory=True)
+        b.copy_(bases_d)
+        o = torch.empty(len(offsets_np), dtype=torch.int64, pin_memory=True)
+        o.copy_(torch.from_numpy(offsets_np))
+        return cls(b, o, torch.empty((n_rows, k), dtype=torch.int32, pin_memory=True),
+                   torch.empty((n_rows, k), dtype=torch.float32, pin_memory=True))
+
+    @property
+    def h2d_bytes(self) -> int:
+        return self.bases.numel() + 8 * self.offsets.numel()
+
+    @property
+    def d2h_bytes(self) -> int:
+        return 4 * self.nbr_idx.numel() + 4 * self.nbr_dist.numel()
+
+
+def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *, mode: int = 0, group=None,
+                      timers: StageTimes | None = None) -> HotPathResult:
+    """The call a host program makes: reads in pinned host memory -> device ->
+    extract/project/kNN -> neighbour lists back in pinned host memory.  Returns
+    after the results have landed."""
+    dev = torch.device("cuda", eng.device)
+    n = hb.bases.numel()
+    bases_d = torch.empty(n + 16, dtype=torch.uint8, device=dev)[:n]
+    bases_d.copy_(hb.bases, non_blocking=True)
+    offsets_d = hb.offsets.to(dev, non_blocking=True)
+    res = run_hot_path(eng, bases_d, offsets_d, P_dev, nk, k_nn, mode=mode, timers=timers, group=group)
+    hb.nbr_idx[:, : res.nbr_idx.shape[1]].copy_(res.nbr_idx, non_blocking=True)
+    hb.nbr_dist[:, : res.nbr_dist.shape[1]].copy_(res.nbr_dist, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return res

@@ -40,6 +40,14 @@ const char *fr_last_error(const fr_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py: gpu_launches) */
 int64_t fr_launch_count(const fr_ctx *ctx);
 
+/* Per-kernel device timing (bench.py: roofline.achieved).  While enabled every
+ * kernel launch of this context is bracketed by a CUDA event pair on its
+ * stream.  fr_profile_read waits for the recorded events, writes one line
+ * "<kernel> <launches> <total_ms>\n" per kernel into buf (NUL-terminated,
+ * truncated to cap; *len_out = full length) and clears the records. */
+int fr_profile_enable(fr_ctx *ctx, int on);
+int fr_profile_read(fr_ctx *ctx, char *buf, int64_t cap, int64_t *len_out);
+
 /* ---- host-side parsers (native equivalents of the reference's C++ I/O) ---- */
 
 /* kmer_searcher.cpp:259-273.  Whitespace-separated tokens; wrong-length,

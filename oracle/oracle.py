@@ -257,3 +257,49 @@ def parse_fastx(text: bytes):
     if not is_fastq and cur_id:
         out.append((cur_id.decode(), b"".join(cur_seq)))
     return out
+
+
+# ---------------------------------------------------------------------------
+# multi-core legs for bench.py's CPU baseline (same arithmetic, all host cores)
+# ---------------------------------------------------------------------------
+def project_threads(indptr, indices, P_csr, nk: int, threads: int) -> np.ndarray:
+    """project() over `threads` OS threads (ctypes releases the GIL); rows are
+    independent, so the result is bit-identical to project()."""
+    from concurrent.futures import ThreadPoolExecutor
+    indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+    R = len(indptr) - 1
+    if threads <= 1 or R < 2 * threads:
+        return project(indptr, indices, P_csr, nk)
+    P_csr = P_csr.tocsr()
+    bounds = np.linspace(0, R, threads + 1).astype(np.int64)
+
+    def work(t):
+        a, b = int(bounds[t]), int(bounds[t + 1])
+        ip = indptr[a:b + 1] - indptr[a]
+        return project(ip, indices[indptr[a]:indptr[b]], P_csr, nk)
+
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(work, range(threads)))
+    return np.concatenate(parts, axis=0)
+
+
+def knn_blas(Xn: np.ndarray, norms: np.ndarray, q0: int, q1: int, k: int, block: int = 2048):
+    """Exact cosine kNN of unit rows [q0,q1) against all rows with BLAS sgemm
+    (all host threads) + partial sort; same definition as knn(): dist = 1 - dot,
+    zero-norm rows at distance 1, ties by lower index."""
+    N = Xn.shape[0]
+    idx = np.zeros((q1 - q0, k), dtype=np.int32)
+    dist = np.zeros((q1 - q0, k), dtype=np.float32)
+    zero_db = norms == 0
+    for a in range(q0, q1, block):
+        b = min(q1, a + block)
+        d = 1.0 - Xn[a:b] @ Xn.T
+        d[:, zero_db] = 1.0
+        d[norms[a:b] == 0, :] = 1.0
+        kk = min(k, N)
+        part = np.argpartition(d, kk - 1, axis=1)[:, :kk]
+        pd = np.take_along_axis(d, part, axis=1)
+        order = np.lexsort((part, pd), axis=1)
+        idx[a - q0:b - q0, :kk] = np.take_along_axis(part, order, axis=1)
+        dist[a - q0:b - q0, :kk] = np.take_along_axis(pd, order, axis=1)
+    return idx, dist
