@@ -66,6 +66,8 @@ struct fr_ctx {
     void *d_knn_ws = nullptr;
     int64_t knn_ws_cap = 0;
     int64_t knn_fallback_rows = 0;
+    bool knn_fb_pending = false;    // h_counters[4] holds the count once knn_fb_stream has drained
+    cudaStream_t knn_fb_stream = nullptr;
 };
 
 int fr_fail(fr_ctx *ctx, int code, const char *what);

@@ -18,6 +18,7 @@ extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const fl
     if (nq == 0) return FR_OK;
     FR_CUDA(ctx, cudaSetDevice(ctx->device));
     ctx->knn_fallback_rows = 0;
+    ctx->knn_fb_pending = false;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == 1)
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
@@ -27,4 +28,13 @@ extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const fl
     return fr_knn_tc_launch(ctx, d_En, d_Eh, d_norms, n_db, D, Dp, q0, nq, k, d_idx, d_dist, st);
 }
 
-extern "C" int64_t fr_knn_last_fallback_rows(const fr_ctx *ctx) { return ctx ? ctx->knn_fallback_rows : 0; }
+extern "C" int64_t fr_knn_last_fallback_rows(fr_ctx *ctx) {
+    if (!ctx) return 0;
+    if (ctx->knn_fb_pending) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->knn_fb_stream);
+        ctx->knn_fallback_rows = (int64_t)ctx->h_counters[4];
+        ctx->knn_fb_pending = false;
+    }
+    return ctx->knn_fallback_rows;
+}

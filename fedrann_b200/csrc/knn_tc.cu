@@ -1,10 +1,612 @@
-// placeholder replaced by the tcgen05 kernel (see git history): routes to the exact scan
+// K6 + K7 -- blocked exact cosine kNN on the tcgen05 tensor cores.
+// Replaces NNDescent_ava.get_neighbors (fedrann/nearest_neighbors.py:22-55,
+// called with the constants of fedrann/__main__.py:184-197) by an EXACT search.
+//
+// K6  fr_knn_tc_kernel: S = Q . DB^T on tcgen05.mma (fp16 operands, fp32
+//     accumulators in TMEM), 128 query rows x 256 database rows per tile.  The
+//     query tile stays resident in shared memory, database tiles stream through
+//     a TMA/mbarrier ring, and the accumulator is double-buffered in TMEM so the
+//     epilogue of tile i overlaps the MMAs of tile i+1.  The epilogue never
+//     writes S: every thread owns one query row (one TMEM lane), compares the
+//     scores against that row's running threshold and appends the few survivors
+//     to the row's candidate buffer; when a buffer fills the warp selects its
+//     best CAP/2 entries exactly (bitwise binary search + ballot compaction) and
+//     raises the threshold.  Everything a row ever dropped scored <= its final
+//     threshold.
+// K7  fr_knn_rerank_kernel: per query row, merges its candidate buffers, keeps
+//     the CAP/2 best approximate scores, recomputes those in fp32 with the SAME
+//     summation order as the exact scan (knn_exact.cu), sorts, and certifies the
+//     row: the k-th exact similarity must exceed every dropped candidate's
+//     approximate score by more than the fp16 rounding bound.  Rows that cannot
+//     be certified are re-done by the exact scan, so the result never depends
+//     on fp16 rounding.
 #include "common.cuh"
+
+#include <cuda.h>
+
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
                         int32_t *d_idx, float *d_dist, cudaStream_t st);
+
+namespace {
+
+constexpr int TC_M = 128;                        // query rows per tile (TMEM lanes)
+constexpr int TC_N = 256;                        // database rows per tile (TMEM columns)
+constexpr int TC_KB = 64;                        // K elements per smem block: 128 B = one swizzle row
+constexpr int TC_THREADS = 192;                  // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int TC_ABLK = TC_M * TC_KB * 2;        // 16 KB per resident A block
+constexpr int TC_STAGE = TC_N * TC_KB * 2;       // 32 KB per B stage
+constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_MAX_KBLKS = 8;                  // Dp <= 512 keeps the query tile resident
+constexpr int TC_MAX_SLOTS = 6;
+constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_N >> 3) << 17) | ((TC_M >> 4) << 24);  // f16 x f16, K-major
+
+// |fp16-operand score - fp32 score| for unit rows: 2^-10 (two roundings, Cauchy-Schwarz) + fp32
+// accumulation of <= 512 terms + subnormal inputs; see DESIGN.md "kNN certification".
+constexpr float TC_EPS = 1.1e-3f;
+
+struct TcParams {
+    int64_t n_db, nq, q0;
+    int kblks, stages;
+    int64_t db_tiles, q_tiles, units;
+    int n_ctas, slots, kprime;
+    unsigned long long *keys;
+    int *counts;
+    float *thrs;
+    const float *norms;
+};
+
+// ---------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate)
+        : "memory");
+}
+// K-major operand, 128-byte swizzle: 8-row groups 1024 B apart, descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
+    return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// float <-> unsigned with the same ordering
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t u = __float_as_uint(f);
+    return u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) {
+    return __uint_as_float(u ^ ((u >> 31) ? 0x80000000u : 0xFFFFFFFFu));
+}
+// bigger key = better candidate: higher score first, then lower database index
+__device__ __forceinline__ unsigned long long tc_key(float score, uint32_t idx) {
+    return ((unsigned long long)f2ord(score) << 32) | (unsigned long long)(0xFFFFFFFFu - idx);
+}
+
+// Warp-cooperative exact selection: keeps the `keep` largest of the n 64-bit keys at buf[0..n)
+// (n <= 32*KPL, keys distinct), compacted to buf[0..keep); returns the float score of the
+// smallest kept key.  All 32 lanes call it with the same arguments.
+template <int KPL>
+__device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n, int keep) {
+    const int lane = threadIdx.x & 31;
+    uint32_t hi[KPL], lo[KPL];
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+        const int j = lane + 32 * i;
+        unsigned long long key = j < n ? __ldcg(buf + j) : 0ull;
+        hi[i] = (uint32_t)(key >> 32);
+        lo[i] = (uint32_t)key;
+    }
+    uint32_t T = 0;
+    for (int b = 31; b >= 0; --b) {
+        const uint32_t cand = T | (1u << b);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) c += hi[i] >= cand;
+        if (__reduce_add_sync(0xFFFFFFFFu, c) >= keep) T = cand;
+    }
+    int cgt = 0, ceq = 0;
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) { cgt += hi[i] > T; ceq += hi[i] == T; }
+    cgt = __reduce_add_sync(0xFFFFFFFFu, cgt);
+    ceq = __reduce_add_sync(0xFFFFFFFFu, ceq);
+    const int need = keep - cgt;  // >= 1 entries wanted among the ties at T
+    uint32_t U = 0;
+    if (ceq > need) {
+        for (int b = 31; b >= 0; --b) {
+            const uint32_t cand = U | (1u << b);
+            int c = 0;
+#pragma unroll
+            for (int i = 0; i < KPL; ++i) c += (hi[i] == T) && (lo[i] >= cand);
+            if (__reduce_add_sync(0xFFFFFFFFu, c) >= need) U = cand;
+        }
+    }
+    __syncwarp();
+    int pos = 0;
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+        const bool kp = hi[i] > T || (hi[i] == T && lo[i] >= U && hi[i] != 0);
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, kp);
+        if (kp) buf[pos + __popc(m & ((1u << lane) - 1))] = ((unsigned long long)hi[i] << 32) | lo[i];
+        pos += __popc(m);
+    }
+    __syncwarp();
+    return ord2f(T);
+}
+
+// the CTA that owns unit u of the linearised (query tile, database tile) space
+__device__ __forceinline__ int tc_owner(int64_t u, int64_t units, int n_ctas) {
+    return (int)(((u + 1) * n_ctas - 1) / units);
+}
+
+// ---------------------------------------------------------------- K6
+template <int CAP>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
+    extern __shared__ unsigned char tc_smem_raw[];
+    const uint32_t raw = smem_u32(tc_smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    unsigned char *gbase = tc_smem_raw + (base - raw);
+    const uint32_t sA = base;
+    const uint32_t sB = sA + p.kblks * TC_ABLK;
+    const uint32_t sBar = sB + p.stages * TC_STAGE;
+    // barriers: full[8] empty[8] a_full a_empty tmem_full[2] tmem_empty[2], then the TMEM base address
+    const uint32_t bFull = sBar, bEmpty = sBar + 64, bAFull = sBar + 128, bAEmpty = sBar + 136,
+                   bTFull = sBar + 144, bTEmpty = sBar + 160;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gbase + (sBar - base) + 176);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(bFull + 8 * s, 1); mbar_init(bEmpty + 8 * s, 1); }
+        mbar_init(bAFull, 1);
+        mbar_init(bAEmpty, 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(bTFull + 8 * b, 1); mbar_init(bTEmpty + 8 * b, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32((const void *)tmem_slot)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    const int cta = blockIdx.x;
+    const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
+    const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
+
+    if (warp == 0) {
+        // ------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0, seg = 0;
+            for (int64_t u = u_begin; u < u_end;) {
+                const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
+                const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
+                if (seg > 0) mbar_wait(bAEmpty, (seg - 1) & 1);   // previous segment's MMAs are done with A
+                mbar_expect_tx(bAFull, (uint32_t)p.kblks * TC_ABLK);
+                for (int kb = 0; kb < p.kblks; ++kb)
+                    tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
+                for (int64_t t = t0; t < t1; ++t) {
+                    for (int kb = 0; kb < p.kblks; ++kb) {
+                        mbar_wait(bEmpty + 8 * stage, phase ^ 1);
+                        mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
+                        const uint32_t dst = sB + stage * TC_STAGE;
+                        tma_load_2d(dst, &tmap, bFull + 8 * stage, kb * TC_KB, (int)(t * TC_N));
+                        tma_load_2d(dst + TC_STAGE / 2, &tmap, bFull + 8 * stage, kb * TC_KB,
+                                    (int)(t * TC_N + TC_N / 2));
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+                u += t1 - t0;
+                ++seg;
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0, seg = 0, tile = 0;
+            for (int64_t u = u_begin; u < u_end;) {
+                const int64_t t0 = u % p.db_tiles;
+                const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
+                mbar_wait(bAFull, seg & 1);
+                for (int64_t t = t0; t < t1; ++t, ++tile) {
+                    const uint32_t buf = tile & 1;
+                    mbar_wait(bTEmpty + 8 * buf, ((tile >> 1) & 1) ^ 1);   // epilogue drained this accumulator
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem + buf * TC_N;
+                    for (int kb = 0; kb < p.kblks; ++kb) {
+                        mbar_wait(bFull + 8 * stage, phase);
+                        tc_fence_after();
+                        const uint64_t ad = tc_smem_desc(sA + kb * TC_ABLK);
+                        const uint64_t bd = tc_smem_desc(sB + stage * TC_STAGE);
+#pragma unroll
+                        for (int k = 0; k < TC_KB / 16; ++k)
+                            tc_mma(d_tmem, ad + 2 * k, bd + 2 * k, (kb | k) != 0);   // +32 B per K=16 step
+                        tc_commit(bEmpty + 8 * stage);                               // frees the stage when read
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                    tc_commit(bTFull + 8 * buf);                                     // accumulator complete
+                }
+                tc_commit(bAEmpty);
+                u += t1 - t0;
+                ++seg;
+            }
+        }
+    } else {
+        // ------------------------------------------------ epilogue: threshold filter + candidate buffers
+        const int quad = warp & 3;                       // TMEM lanes 32*quad .. 32*quad+31
+        const int row_in_tile = quad * 32 + lane;
+        uint32_t tile = 0;
+        for (int64_t u = u_begin; u < u_end;) {
+            const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
+            const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
+            const int slot = cta - tc_owner(qt * p.db_tiles, p.units, p.n_ctas);
+            const int64_t grow = qt * TC_M + row_in_tile;
+            const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
+            const int64_t stream = (valid ? grow : 0) * p.slots + slot;
+            unsigned long long *buf = p.keys + stream * CAP;
+            int count = 0;
+            float thr = valid ? -INFINITY : INFINITY;
+            for (int64_t t = t0; t < t1; ++t, ++tile) {
+                const uint32_t ab = tile & 1;
+                mbar_wait(bTFull + 8 * ab, (tile >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
+                const int64_t col0 = t * TC_N;
+                const bool ragged = col0 + TC_N > p.n_db;
+#pragma unroll 1
+                for (int c = 0; c < TC_N / 32; ++c) {
+                    uint32_t v[32];
+                    tc_ld32(taddr + c * 32, v);
+                    tc_ld_wait();
+                    const uint32_t cbase = (uint32_t)(col0 + c * 32);
+                    if (!ragged) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float f = __uint_as_float(v[j]);
+                            if (f > thr) { buf[count] = tc_key(f, cbase + j); ++count; }
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float f = __uint_as_float(v[j]);
+                            if (f > thr && (int64_t)cbase + j < p.n_db) { buf[count] = tc_key(f, cbase + j); ++count; }
+                        }
+                    }
+                    // a buffer that could overflow during the next 32 columns is compacted now
+                    unsigned need = __ballot_sync(0xFFFFFFFFu, count > CAP - 32);
+                    while (need) {
+                        const int src = __ffs(need) - 1;
+                        need &= need - 1;
+                        const int n = __shfl_sync(0xFFFFFFFFu, count, src);
+                        const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
+                        __syncwarp();
+                        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n,
+                                                                  p.kprime);
+                        if (lane == src) { thr = nt; count = p.kprime; }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
+            }
+            if (valid) { p.counts[stream] = count; p.thrs[stream] = thr; }
+            u += t1 - t0;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------- K7
+constexpr int RR_WARPS = 4;
+
+// ascending bitonic sort of n_pow2 keys in shared memory by one warp
+__device__ void rr_warp_sort(unsigned long long *a, int n_pow2) {
+    const int lane = threadIdx.x & 31;
+    for (int k = 2; k <= n_pow2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < n_pow2; i += 32) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const unsigned long long x = a[i], y = a[ixj];
+                    const bool up = (i & k) == 0;
+                    if ((x > y) == up) { a[i] = y; a[ixj] = x; }
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+template <int CAP>
+__global__ void __launch_bounds__(RR_WARPS * 32)
+fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
+                     int64_t nq, int k, int slots, const unsigned long long *__restrict__ keys,
+                     const int *__restrict__ counts, const float *__restrict__ thrs, int32_t *__restrict__ out_idx,
+                     float *__restrict__ out_dist, int32_t *__restrict__ fb_rows, unsigned long long *fb_count) {
+    constexpr int KEEP = CAP / 2;
+    extern __shared__ __align__(16) unsigned char rr_smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t per_warp = (size_t)slots * CAP * 8 + (size_t)KEEP * 8 * 2;
+    unsigned long long *cand = reinterpret_cast<unsigned long long *>(rr_smem + warp * per_warp);
+    unsigned long long *res = cand + (size_t)slots * CAP;        // [KEEP] sorted (dist, idx) keys; power of two
+    for (int64_t row = (int64_t)blockIdx.x * RR_WARPS + warp; row < nq; row += (int64_t)gridDim.x * RR_WARPS) {
+        const float qn = norms[q0 + row];
+        if (qn == 0.0f) {   // zero-norm query: distance 1 to everything, ties by lower index
+            for (int j = lane; j < k; j += 32) { out_idx[row * k + j] = j; out_dist[row * k + j] = 1.0f; }
+            continue;
+        }
+        // ---- merge this row's candidate buffers
+        int n = 0;
+        float tau = -INFINITY;
+        for (int s = 0; s < slots; ++s) {
+            const int c = counts[row * slots + s];
+            if (c == 0) continue;
+            tau = fmaxf(tau, thrs[row * slots + s]);
+            const unsigned long long *src = keys + (row * slots + s) * CAP;
+            for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + i);
+            n += c;
+        }
+        __syncwarp();
+        // ---- keep the KEEP best approximate scores (exact selection on the 64-bit keys)
+        int m = n;
+        if (n > KEEP) {
+            uint32_t T = 0;
+            for (int b = 31; b >= 0; --b) {
+                const uint32_t cd = T | (1u << b);
+                int c = 0;
+                for (int i = lane; i < n; i += 32) c += (uint32_t)(cand[i] >> 32) >= cd;
+                if (__reduce_add_sync(0xFFFFFFFFu, c) >= KEEP) T = cd;
+            }
+            int cgt = 0, ceq = 0;
+            for (int i = lane; i < n; i += 32) {
+                const uint32_t h = (uint32_t)(cand[i] >> 32);
+                cgt += h > T;
+                ceq += h == T;
+            }
+            cgt = __reduce_add_sync(0xFFFFFFFFu, cgt);
+            ceq = __reduce_add_sync(0xFFFFFFFFu, ceq);
+            const int need = KEEP - cgt;
+            uint32_t U = 0;
+            if (ceq > need) {
+                for (int b = 31; b >= 0; --b) {
+                    const uint32_t cd = U | (1u << b);
+                    int c = 0;
+                    for (int i = lane; i < n; i += 32)
+                        c += ((uint32_t)(cand[i] >> 32) == T) && ((uint32_t)cand[i] >= cd);
+                    if (__reduce_add_sync(0xFFFFFFFFu, c) >= need) U = cd;
+                }
+            }
+            // compact in place, front to back (a write never passes the read position)
+            int pos = 0;
+            for (int i0 = 0; i0 < n; i0 += 32) {
+                const int i = i0 + lane;
+                unsigned long long key = i < n ? cand[i] : 0ull;
+                const uint32_t h = (uint32_t)(key >> 32), l = (uint32_t)key;
+                const bool kp = i < n && (h > T || (h == T && l >= U));
+                const unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
+                __syncwarp();
+                if (kp) cand[pos + __popc(bal & ((1u << lane) - 1))] = key;
+                pos += __popc(bal);
+                __syncwarp();
+            }
+            m = pos;
+            tau = fmaxf(tau, ord2f(T));
+        }
+        // ---- exact fp32 similarities, same summation order as fr_knn_exact_kernel
+        float q[16];
+        const float *qp = En + (q0 + row) * D;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { const int j = lane + 32 * i; q[i] = j < D ? qp[j] : 0.0f; }
+        for (int c0 = 0; c0 < m; c0 += 4) {
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            uint32_t id[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) id[u] = 0xFFFFFFFFu - (uint32_t)cand[min(c0 + u, m - 1)];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int j = lane + 32 * i;
+                if (j < D) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) acc[u] = fmaf(q[i], __ldg(En + (int64_t)id[u] * D + j), acc[u]);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                for (int s = 16; s > 0; s >>= 1) acc[u] += __shfl_xor_sync(0xFFFFFFFFu, acc[u], s);
+            if (lane < 4 && c0 + lane < m) {
+                const float a = lane == 0 ? acc[0] : lane == 1 ? acc[1] : lane == 2 ? acc[2] : acc[3];
+                const uint32_t ii = lane == 0 ? id[0] : lane == 1 ? id[1] : lane == 2 ? id[2] : id[3];
+                const float d = norms[ii] == 0.0f ? 1.0f : 1.0f - a;
+                res[c0 + lane] = ((unsigned long long)f2ord(d) << 32) | ii;   // ascending (dist, idx)
+            }
+        }
+        for (int i = m + lane; i < KEEP; i += 32) res[i] = 0xFFFFFFFFFFFFFFFFull;
+        __syncwarp();
+        rr_warp_sort(res, KEEP);
+        for (int j = lane; j < k; j += 32) {
+            const unsigned long long key = res[j];
+            out_idx[row * k + j] = j < m ? (int32_t)(uint32_t)key : -1;
+            out_dist[row * k + j] = j < m ? ord2f((uint32_t)(key >> 32)) : INFINITY;
+        }
+        // ---- certification: nothing dropped can beat the k-th exact neighbour
+        if (lane == 0) {
+            bool ok = m >= k;
+            if (ok && tau > -INFINITY) {
+                const float dk = ord2f((uint32_t)(res[k - 1] >> 32));
+                ok = dk < 1.0f - (tau + TC_EPS);
+            }
+            if (!ok) fb_rows[atomicAdd(fb_count, 1ull)] = (int32_t)row;
+        }
+        __syncwarp();
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+template <int CAP>
+int tc_run(fr_ctx *ctx, const CUtensorMap &tmap, const TcParams &p, size_t smem, const float *d_En,
+           const float *d_norms, int D, int k, int32_t *d_idx, float *d_dist, int32_t *fb_rows,
+           unsigned long long *fb_count, cudaStream_t st) {
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
+    fr_knn_tc_kernel<CAP><<<p.n_ctas, TC_THREADS, smem, st>>>(tmap, p);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
+    const size_t rsmem = (size_t)RR_WARPS * ((size_t)p.slots * CAP * 8 + (size_t)(CAP / 2) * 16);
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)rsmem));
+    int64_t blocks = (p.nq + RR_WARPS - 1) / RR_WARPS;
+    if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
+    fr_kt_begin(ctx, "fr_knn_rerank_kernel", st);
+    fr_knn_rerank_kernel<CAP><<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
+        d_En, d_norms, p.n_db, D, p.q0, p.nq, k, p.slots, p.keys, p.counts, p.thrs, d_idx, d_dist, fb_rows, fb_count);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_rerank_kernel");
+    return FR_OK;
+}
+
+}  // namespace
+
 int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
                      int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
-    (void)d_Eh; (void)Dp;
-    return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
+    // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
+    if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N)
+        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
+    EncodeTiledFn encode = get_encode_fn();
+    if (!encode) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled is not available");
+    const int cap = k <= 32 ? 128 : (k <= 64 ? 256 : 512);
+
+    TcParams p{};
+    p.n_db = n_db; p.nq = nq; p.q0 = q0;
+    p.kblks = Dp / TC_KB;
+    const size_t fixed = 1024 + 256 + (size_t)p.kblks * TC_ABLK;
+    int stages = (int)((232448 - fixed) / TC_STAGE);
+    p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
+    const size_t smem = fixed + (size_t)p.stages * TC_STAGE;
+    p.db_tiles = (n_db + TC_N - 1) / TC_N;
+    p.q_tiles = (nq + TC_M - 1) / TC_M;
+    p.units = p.db_tiles * p.q_tiles;
+    int64_t n_ctas = ctx->sm_count;
+    if (n_ctas > 4 * p.q_tiles) n_ctas = 4 * p.q_tiles;
+    if (n_ctas > p.units) n_ctas = p.units;
+    p.n_ctas = (int)n_ctas;
+    p.slots = 1;   // most CTAs that share one query tile (exact, same arithmetic as tc_owner)
+    for (int64_t qt = 0; qt < p.q_tiles; ++qt) {
+        const int64_t a = ((qt * p.db_tiles + 1) * n_ctas - 1) / p.units;
+        const int64_t b = (((qt + 1) * p.db_tiles) * n_ctas - 1) / p.units;
+        if ((int)(b - a + 1) > p.slots) p.slots = (int)(b - a + 1);
+    }
+    if (p.slots > TC_MAX_SLOTS) return fr_fail(ctx, FR_ERR_STATE, "fr_knn: internal slot bound exceeded");
+    p.kprime = cap / 2;
+    p.norms = d_norms;
+
+    // workspace: keys | counts | thrs | fallback rows | fallback counter
+    const int64_t streams = nq * p.slots;
+    const size_t keys_b = (size_t)streams * cap * 8, cnt_b = ((size_t)streams * 4 + 15) & ~(size_t)15;
+    const size_t need = keys_b + 2 * cnt_b + (((size_t)nq * 4 + 15) & ~(size_t)15) + 16;
+    int rc = fr_ensure(ctx, &ctx->d_knn_ws, &ctx->knn_ws_cap, (int64_t)need, "kNN workspace");
+    if (rc) return rc;
+    unsigned char *ws = (unsigned char *)ctx->d_knn_ws;
+    p.keys = (unsigned long long *)ws;
+    p.counts = (int *)(ws + keys_b);
+    p.thrs = (float *)(ws + keys_b + cnt_b);
+    int32_t *fb_rows = (int32_t *)(ws + keys_b + 2 * cnt_b);
+    unsigned long long *fb_count = (unsigned long long *)(ws + need - 16);
+    FR_CUDA(ctx, cudaMemsetAsync(p.counts, 0, cnt_b, st));
+    FR_CUDA(ctx, cudaMemsetAsync(fb_count, 0, 16, st));
+
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {(cuuint64_t)Dp, (cuuint64_t)n_db};
+    const cuuint64_t gstr[1] = {(cuuint64_t)Dp * 2};
+    const cuuint32_t box[2] = {TC_KB, TC_M};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(d_Eh), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled failed");
+
+    if (cap == 128)
+        rc = tc_run<128>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
+    else if (cap == 256)
+        rc = tc_run<256>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
+    else
+        rc = tc_run<512>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
+    if (rc) return rc;
+    // rows the certificate rejected: exact scan (reads the row list and its length on the device)
+    rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, d_idx, d_dist, st);
+    if (rc) return rc;
+    FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[4], fb_count, 8, cudaMemcpyDeviceToHost, st));
+    ctx->knn_fb_pending = true;
+    ctx->knn_fb_stream = st;
+    return FR_OK;
 }

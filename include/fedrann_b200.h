@@ -110,7 +110,7 @@ int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norm
            int D, int Dp, int64_t q0, int64_t nq, int k, int mode, int32_t *d_idx, float *d_dist,
            void *stream);
 /* statistics of the last fr_knn call: rows that needed the exact fallback */
-int64_t fr_knn_last_fallback_rows(const fr_ctx *ctx);
+int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
 
 #ifdef __cplusplus
 }
