@@ -23,6 +23,8 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <cstdio>
+#include <cstdlib>
 
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
@@ -54,6 +56,7 @@ struct TcParams {
     int *counts;
     float *thrs;
     const float *norms;
+    unsigned long long *dbg;   // optional per-role wait-cycle counters (FR_KNN_DEBUG=1)
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -79,6 +82,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "r"(bar), "r"(parity)
             : "memory");
     } while (!ok);
+}
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, long long &acc, bool on) {
+    if (!on) { mbar_wait(bar, parity); return; }
+    const long long t0 = clock64();
+    mbar_wait(bar, parity);
+    acc += clock64() - t0;
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
     asm volatile(
@@ -130,36 +139,59 @@ __device__ __forceinline__ unsigned long long tc_key(float score, uint32_t idx) 
     return ((unsigned long long)f2ord(score) << 32) | (unsigned long long)(0xFFFFFFFFu - idx);
 }
 
-// Warp-cooperative exact selection: keeps the `keep` largest of the n 64-bit keys at buf[0..n)
-// (n <= 32*KPL, keys distinct), compacted to buf[0..keep); returns the float score of the
-// smallest kept key.  All 32 lanes call it with the same arguments.
+// Warp-cooperative selection on the n 64-bit keys at buf[0..n) (n <= 32*KPL, keys distinct):
+// finds a score threshold T such that the number of keys with score >= T lies in
+// [keep_lo, keep_hi], keeps exactly those keys (compacted to the front of buf) and returns
+// T as a float; *kept receives their number.  The search walks the score bits from the
+// highest bit in which the keys differ and stops as soon as the count falls in the window
+// (a handful of REDUX steps); if ties at T make the window unreachable it falls back to the
+// exact keep_lo largest keys (ties broken by lower database index).  All 32 lanes call it
+// with the same arguments.
 template <int KPL>
-__device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n, int keep) {
+__device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n, int keep_lo, int keep_hi, int *kept) {
     const int lane = threadIdx.x & 31;
     uint32_t hi[KPL], lo[KPL];
+    uint32_t mx = 0, mn = 0xFFFFFFFFu;
 #pragma unroll
     for (int i = 0; i < KPL; ++i) {
         const int j = lane + 32 * i;
         unsigned long long key = j < n ? __ldcg(buf + j) : 0ull;
         hi[i] = (uint32_t)(key >> 32);
         lo[i] = (uint32_t)key;
+        mx = max(mx, hi[i]);
+        if (j < n) mn = min(mn, hi[i]);
     }
-    uint32_t T = 0;
-    for (int b = 31; b >= 0; --b) {
-        const uint32_t cand = T | (1u << b);
-        int c = 0;
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+    const uint32_t diff = mx ^ mn;
+    uint32_t T = mn;          // count(score >= mn) = n >= keep_lo
+    int tot_T = n;
+    bool in_window = n <= keep_hi;
+    if (diff != 0 && !in_window) {
+        const int b0 = 31 - __clz(diff);
+        T = b0 == 31 ? 0u : (mx >> (b0 + 1)) << (b0 + 1);   // common prefix; count(score >= T) = n
+        for (int b = b0; b >= 0; --b) {
+            const uint32_t cand = T | (1u << b);
+            int c = 0;
 #pragma unroll
-        for (int i = 0; i < KPL; ++i) c += hi[i] >= cand;
-        if (__reduce_add_sync(0xFFFFFFFFu, c) >= keep) T = cand;
+            for (int i = 0; i < KPL; ++i) c += hi[i] >= cand;
+            const int tot = __reduce_add_sync(0xFFFFFFFFu, c);
+            if (tot >= keep_lo) {
+                T = cand;
+                tot_T = tot;
+                if (tot <= keep_hi) { in_window = true; break; }
+            }
+        }
     }
-    int cgt = 0, ceq = 0;
-#pragma unroll
-    for (int i = 0; i < KPL; ++i) { cgt += hi[i] > T; ceq += hi[i] == T; }
-    cgt = __reduce_add_sync(0xFFFFFFFFu, cgt);
-    ceq = __reduce_add_sync(0xFFFFFFFFu, ceq);
-    const int need = keep - cgt;  // >= 1 entries wanted among the ties at T
     uint32_t U = 0;
-    if (ceq > need) {
+    if (!in_window) {
+        // more than keep_hi keys tie at or above T with fewer than keep_lo strictly above: keep the
+        // keep_lo best exactly, breaking the tie at T by database index
+        int cgt = 0;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) cgt += hi[i] > T;
+        cgt = __reduce_add_sync(0xFFFFFFFFu, cgt);
+        const int need = keep_lo - cgt;
         for (int b = 31; b >= 0; --b) {
             const uint32_t cand = U | (1u << b);
             int c = 0;
@@ -172,18 +204,57 @@ __device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n, int
     int pos = 0;
 #pragma unroll
     for (int i = 0; i < KPL; ++i) {
-        const bool kp = hi[i] > T || (hi[i] == T && lo[i] >= U && hi[i] != 0);
+        const bool kp = hi[i] != 0 && (hi[i] > T || (hi[i] == T && lo[i] >= U));
         const unsigned m = __ballot_sync(0xFFFFFFFFu, kp);
         if (kp) buf[pos + __popc(m & ((1u << lane) - 1))] = ((unsigned long long)hi[i] << 32) | lo[i];
         pos += __popc(m);
     }
     __syncwarp();
+    *kept = pos;
+    (void)tot_T;
     return ord2f(T);
 }
 
 // the CTA that owns unit u of the linearised (query tile, database tile) space
 __device__ __forceinline__ int tc_owner(int64_t u, int64_t units, int n_ctas) {
     return (int)(((u + 1) * n_ctas - 1) / units);
+}
+
+// Epilogue inner step: 32 scores of one query row (this thread's TMEM lane) against the row's
+// running threshold.  Groups of 8 are first reduced to their maximum; only when some lane of
+// the warp has a group maximum above its threshold does the warp walk that group's elements.
+// Survivors are appended to the row's candidate buffer; a buffer that could overflow during
+// the next 32 columns is compacted by the whole warp (tc_warp_select) and the threshold rises.
+template <int CAP>
+__device__ __forceinline__ void tc_filter32(const uint32_t (&v)[32], uint32_t cbase, bool ragged, int64_t n_db,
+                                            unsigned long long *buf, int &count, float &thr) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        float m = fmaxf(fmaxf(__uint_as_float(v[8 * g]), __uint_as_float(v[8 * g + 1])),
+                        fmaxf(__uint_as_float(v[8 * g + 2]), __uint_as_float(v[8 * g + 3])));
+        m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[8 * g + 4]), __uint_as_float(v[8 * g + 5])),
+                           fmaxf(__uint_as_float(v[8 * g + 6]), __uint_as_float(v[8 * g + 7]))));
+        if (__any_sync(0xFFFFFFFFu, m > thr)) {
+#pragma unroll
+            for (int j = 8 * g; j < 8 * g + 8; ++j) {
+                const float f = __uint_as_float(v[j]);
+                if (f > thr && (!ragged || (int64_t)cbase + j < n_db)) { buf[count] = tc_key(f, cbase + j); ++count; }
+            }
+        }
+    }
+    unsigned need = __ballot_sync(0xFFFFFFFFu, count > CAP - 32);
+    while (need) {
+        const int lane = threadIdx.x & 31;
+        const int src = __ffs(need) - 1;
+        need &= need - 1;
+        const int n = __shfl_sync(0xFFFFFFFFu, count, src);
+        const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
+        __syncwarp();
+        int kept;
+        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n, 3 * CAP / 8,
+                                                  5 * CAP / 8, &kept);
+        if (lane == src) { thr = nt; count = kept; }
+    }
 }
 
 // ---------------------------------------------------------------- K6
@@ -222,6 +293,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     const uint32_t tmem = *tmem_slot;
 
     const int cta = blockIdx.x;
+    const bool dbg_on = p.dbg != nullptr;
+    long long w0 = 0, w1 = 0;
+    const long long t_start = clock64();
     const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
     const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
 
@@ -239,7 +313,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
                 for (int64_t t = t0; t < t1; ++t) {
                     for (int kb = 0; kb < p.kblks; ++kb) {
-                        mbar_wait(bEmpty + 8 * stage, phase ^ 1);
+                        mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
                         mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
                         const uint32_t dst = sB + stage * TC_STAGE;
                         tma_load_2d(dst, &tmap, bFull + 8 * stage, kb * TC_KB, (int)(t * TC_N));
@@ -263,11 +337,11 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 mbar_wait(bAFull, seg & 1);
                 for (int64_t t = t0; t < t1; ++t, ++tile) {
                     const uint32_t buf = tile & 1;
-                    mbar_wait(bTEmpty + 8 * buf, ((tile >> 1) & 1) ^ 1);   // epilogue drained this accumulator
+                    mbar_wait_t(bTEmpty + 8 * buf, ((tile >> 1) & 1) ^ 1, w1, dbg_on);   // epilogue drained this accumulator
                     tc_fence_after();
                     const uint32_t d_tmem = tmem + buf * TC_N;
                     for (int kb = 0; kb < p.kblks; ++kb) {
-                        mbar_wait(bFull + 8 * stage, phase);
+                        mbar_wait_t(bFull + 8 * stage, phase, w0, dbg_on);
                         tc_fence_after();
                         const uint64_t ad = tc_smem_desc(sA + kb * TC_ABLK);
                         const uint64_t bd = tc_smem_desc(sB + stage * TC_STAGE);
@@ -301,42 +375,21 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             float thr = valid ? -INFINITY : INFINITY;
             for (int64_t t = t0; t < t1; ++t, ++tile) {
                 const uint32_t ab = tile & 1;
-                mbar_wait(bTFull + 8 * ab, (tile >> 1) & 1);
+                mbar_wait_t(bTFull + 8 * ab, (tile >> 1) & 1, w0, dbg_on);
                 tc_fence_after();
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
                 const int64_t col0 = t * TC_N;
                 const bool ragged = col0 + TC_N > p.n_db;
+                uint32_t va[32], vb[32];
+                tc_ld32(taddr, va);
 #pragma unroll 1
-                for (int c = 0; c < TC_N / 32; ++c) {
-                    uint32_t v[32];
-                    tc_ld32(taddr + c * 32, v);
+                for (int c = 0; c < TC_N / 32; c += 2) {
+                    tc_ld_wait();                                   // va landed
+                    tc_ld32(taddr + (c + 1) * 32, vb);              // next chunk in flight while va is filtered
+                    tc_filter32<CAP>(va, (uint32_t)(col0 + c * 32), ragged, p.n_db, buf, count, thr);
                     tc_ld_wait();
-                    const uint32_t cbase = (uint32_t)(col0 + c * 32);
-                    if (!ragged) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float f = __uint_as_float(v[j]);
-                            if (f > thr) { buf[count] = tc_key(f, cbase + j); ++count; }
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float f = __uint_as_float(v[j]);
-                            if (f > thr && (int64_t)cbase + j < p.n_db) { buf[count] = tc_key(f, cbase + j); ++count; }
-                        }
-                    }
-                    // a buffer that could overflow during the next 32 columns is compacted now
-                    unsigned need = __ballot_sync(0xFFFFFFFFu, count > CAP - 32);
-                    while (need) {
-                        const int src = __ffs(need) - 1;
-                        need &= need - 1;
-                        const int n = __shfl_sync(0xFFFFFFFFu, count, src);
-                        const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
-                        __syncwarp();
-                        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n,
-                                                                  p.kprime);
-                        if (lane == src) { thr = nt; count = p.kprime; }
-                    }
+                    if (c + 2 < TC_N / 32) tc_ld32(taddr + (c + 2) * 32, va);
+                    tc_filter32<CAP>(vb, (uint32_t)(col0 + (c + 1) * 32), ragged, p.n_db, buf, count, thr);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -345,6 +398,15 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             if (valid) { p.counts[stream] = count; p.thrs[stream] = thr; }
             u += t1 - t0;
         }
+    }
+    if (dbg_on && lane == 0) {
+        // [0] producer waits for a free stage, [1] MMA waits for data, [2] MMA waits for a drained accumulator,
+        // [3] epilogue (4 warps) waits for an accumulator, [4] epilogue busy, [5] CTA lifetime
+        const long long life = clock64() - t_start;
+        if (warp == 0) atomicAdd(&p.dbg[0], (unsigned long long)w0);
+        else if (warp == 1) { atomicAdd(&p.dbg[1], (unsigned long long)w0); atomicAdd(&p.dbg[2], (unsigned long long)w1); }
+        else { atomicAdd(&p.dbg[3], (unsigned long long)w0); atomicAdd(&p.dbg[4], (unsigned long long)(life - w0)); }
+        if (warp == 0) atomicAdd(&p.dbg[5], (unsigned long long)life);
     }
     tc_fence_before();
     __syncthreads();
@@ -585,6 +647,13 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     FR_CUDA(ctx, cudaMemsetAsync(p.counts, 0, cnt_b, st));
     FR_CUDA(ctx, cudaMemsetAsync(fb_count, 0, 16, st));
 
+    static const bool dbg_env = getenv("FR_KNN_DEBUG") != nullptr;
+    static unsigned long long *d_dbg = nullptr;
+    if (dbg_env) {
+        if (!d_dbg) cudaMalloc(&d_dbg, 64);
+        cudaMemsetAsync(d_dbg, 0, 64, st);
+        p.dbg = d_dbg;
+    }
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)Dp, (cuuint64_t)n_db};
     const cuuint64_t gstr[1] = {(cuuint64_t)Dp * 2};
@@ -602,6 +671,16 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     else
         rc = tc_run<512>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
     if (rc) return rc;
+    if (dbg_env) {
+        unsigned long long h[8];
+        cudaStreamSynchronize(st);
+        cudaMemcpy(h, d_dbg, 64, cudaMemcpyDeviceToHost);
+        const double n = p.n_ctas;
+        fprintf(stderr, "[fr_knn dbg] per-CTA Mcycles: life %.2f | producer wait-empty %.2f | mma wait-data %.2f wait-tmem %.2f"
+                        " | epilogue(avg of 4) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
+                h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / 4e6, h[4] / n / 4e6,
+                (double)p.units / n);
+    }
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
     rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, d_idx, d_dist, st);
     if (rc) return rc;
