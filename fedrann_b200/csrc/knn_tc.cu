@@ -37,11 +37,13 @@ constexpr int TC_N = 256;                        // database rows per tile (TMEM
 constexpr int TC_KB = 64;                        // K elements per smem block: 128 B = one swizzle row
 constexpr int TC_THREADS = 192;                  // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
 constexpr int TC_ABLK = TC_M * TC_KB * 2;        // 16 KB per resident A block
-constexpr int TC_STAGE = TC_N * TC_KB * 2;       // 32 KB per B stage
+constexpr int TC_NS = 128;                       // database rows per B stage / per MMA
+constexpr int TC_STAGE = TC_NS * TC_KB * 2;      // 16 KB per B stage
+constexpr int TC_STASH = 4 * 32 * 32 * 4;        // 16 KB: one 32x32 fp32 chunk per epilogue warp
 constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_MAX_KBLKS = 8;                  // Dp <= 512 keeps the query tile resident
 constexpr int TC_MAX_SLOTS = 6;
-constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_N >> 3) << 17) | ((TC_M >> 4) << 24);  // f16 x f16, K-major
+constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_NS >> 3) << 17) | ((TC_M >> 4) << 24);  // f16 x f16, K-major
 
 // |fp16-operand score - fp32 score| for unit rows: 2^-10 (two roundings, Cauchy-Schwarz) + fp32
 // accumulation of <= 512 terms + subnormal inputs; see DESIGN.md "kNN certification".
@@ -267,7 +269,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     unsigned char *gbase = tc_smem_raw + (base - raw);
     const uint32_t sA = base;
     const uint32_t sB = sA + p.kblks * TC_ABLK;
-    const uint32_t sBar = sB + p.stages * TC_STAGE;
+    const uint32_t sStash = sB + p.stages * TC_STAGE;
+    const uint32_t sBar = sStash + TC_STASH;
     // barriers: full[8] empty[8] a_full a_empty tmem_full[2] tmem_empty[2], then the TMEM base address
     const uint32_t bFull = sBar, bEmpty = sBar + 64, bAFull = sBar + 128, bAEmpty = sBar + 136,
                    bTFull = sBar + 144, bTEmpty = sBar + 160;
@@ -313,13 +316,13 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
                 for (int64_t t = t0; t < t1; ++t) {
                     for (int kb = 0; kb < p.kblks; ++kb) {
-                        mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
-                        mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
-                        const uint32_t dst = sB + stage * TC_STAGE;
-                        tma_load_2d(dst, &tmap, bFull + 8 * stage, kb * TC_KB, (int)(t * TC_N));
-                        tma_load_2d(dst + TC_STAGE / 2, &tmap, bFull + 8 * stage, kb * TC_KB,
-                                    (int)(t * TC_N + TC_N / 2));
-                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                        for (int h = 0; h < TC_N / TC_NS; ++h) {
+                            mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
+                            mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
+                            tma_load_2d(sB + stage * TC_STAGE, &tmap, bFull + 8 * stage, kb * TC_KB,
+                                        (int)(t * TC_N + h * TC_NS));
+                            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                        }
                     }
                 }
                 u += t1 - t0;
@@ -341,15 +344,17 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     tc_fence_after();
                     const uint32_t d_tmem = tmem + buf * TC_N;
                     for (int kb = 0; kb < p.kblks; ++kb) {
-                        mbar_wait_t(bFull + 8 * stage, phase, w0, dbg_on);
-                        tc_fence_after();
                         const uint64_t ad = tc_smem_desc(sA + kb * TC_ABLK);
-                        const uint64_t bd = tc_smem_desc(sB + stage * TC_STAGE);
+                        for (int h = 0; h < TC_N / TC_NS; ++h) {     // two 128-column halves of the accumulator
+                            mbar_wait_t(bFull + 8 * stage, phase, w0, dbg_on);
+                            tc_fence_after();
+                            const uint64_t bd = tc_smem_desc(sB + stage * TC_STAGE);
 #pragma unroll
-                        for (int k = 0; k < TC_KB / 16; ++k)
-                            tc_mma(d_tmem, ad + 2 * k, bd + 2 * k, (kb | k) != 0);   // +32 B per K=16 step
-                        tc_commit(bEmpty + 8 * stage);                               // frees the stage when read
-                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                            for (int k = 0; k < TC_KB / 16; ++k)
+                                tc_mma(d_tmem + h * TC_NS, ad + 2 * k, bd + 2 * k, (kb | k) != 0);   // +32 B per K=16
+                            tc_commit(bEmpty + 8 * stage);                           // frees the stage when read
+                            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                        }
                     }
                     tc_commit(bTFull + 8 * buf);                                     // accumulator complete
                 }
@@ -611,7 +616,7 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     TcParams p{};
     p.n_db = n_db; p.nq = nq; p.q0 = q0;
     p.kblks = Dp / TC_KB;
-    const size_t fixed = 1024 + 256 + (size_t)p.kblks * TC_ABLK;
+    const size_t fixed = 1024 + 256 + TC_STASH + (size_t)p.kblks * TC_ABLK;
     int stages = (int)((232448 - fixed) / TC_STAGE);
     p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
     const size_t smem = fixed + (size_t)p.stages * TC_STAGE;
