@@ -223,25 +223,41 @@ __device__ __forceinline__ int tc_owner(int64_t u, int64_t units, int n_ctas) {
 }
 
 // Epilogue inner step: 32 scores of one query row (this thread's TMEM lane) against the row's
-// running threshold.  Groups of 8 are first reduced to their maximum; only when some lane of
-// the warp has a group maximum above its threshold does the warp walk that group's elements.
+// running threshold.  The chunk maximum is tested first; only when some lane of the warp has a
+// score above its threshold is the chunk stashed in shared memory (float4 per lane, conflict
+// free) and a per-lane hit mask built, after which every lane walks ITS OWN set bits -- the
+// warp's cost is the largest hit count among its lanes, not 32 predicated store sequences.
 // Survivors are appended to the row's candidate buffer; a buffer that could overflow during
 // the next 32 columns is compacted by the whole warp (tc_warp_select) and the threshold rises.
 template <int CAP>
 __device__ __forceinline__ void tc_filter32(const uint32_t (&v)[32], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *buf, int &count, float &thr) {
+                                            unsigned long long *buf, int &count, float &thr, float4 *stash) {
+    float m = -INFINITY;
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        float m = fmaxf(fmaxf(__uint_as_float(v[8 * g]), __uint_as_float(v[8 * g + 1])),
-                        fmaxf(__uint_as_float(v[8 * g + 2]), __uint_as_float(v[8 * g + 3])));
-        m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[8 * g + 4]), __uint_as_float(v[8 * g + 5])),
-                           fmaxf(__uint_as_float(v[8 * g + 6]), __uint_as_float(v[8 * g + 7]))));
-        if (__any_sync(0xFFFFFFFFu, m > thr)) {
+    for (int g = 0; g < 8; ++g)
+        m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
+                           fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]))));
+    if (__any_sync(0xFFFFFFFFu, m > thr)) {
+        uint32_t mask = 0;
 #pragma unroll
-            for (int j = 8 * g; j < 8 * g + 8; ++j) {
-                const float f = __uint_as_float(v[j]);
-                if (f > thr && (!ragged || (int64_t)cbase + j < n_db)) { buf[count] = tc_key(f, cbase + j); ++count; }
-            }
+        for (int g = 0; g < 8; ++g) {
+            stash[g * 32] = make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+                                        __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                mask |= (__uint_as_float(v[4 * g + e]) > thr ? 1u : 0u) << (4 * g + e);
+        }
+        if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
+            const int64_t left = n_db - (int64_t)cbase;
+            mask = left >= 32 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
+        }
+        const float *sf = reinterpret_cast<const float *>(stash);
+        while (mask) {
+            const int j = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const float f = sf[(j >> 2) * 128 + (j & 3)];     // own float4 slot g = j/4, element j%4
+            buf[count] = tc_key(f, cbase + j);
+            ++count;
         }
     }
     unsigned need = __ballot_sync(0xFFFFFFFFu, count > CAP - 32);
@@ -366,6 +382,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     } else {
         // ------------------------------------------------ epilogue: threshold filter + candidate buffers
         const int quad = warp & 3;                       // TMEM lanes 32*quad .. 32*quad+31
+        float4 *stash = reinterpret_cast<float4 *>(gbase + (sStash - base)) + quad * 256 + lane;
         const int row_in_tile = quad * 32 + lane;
         uint32_t tile = 0;
         for (int64_t u = u_begin; u < u_end;) {
@@ -391,10 +408,10 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 for (int c = 0; c < TC_N / 32; c += 2) {
                     tc_ld_wait();                                   // va landed
                     tc_ld32(taddr + (c + 1) * 32, vb);              // next chunk in flight while va is filtered
-                    tc_filter32<CAP>(va, (uint32_t)(col0 + c * 32), ragged, p.n_db, buf, count, thr);
+                    tc_filter32<CAP>(va, (uint32_t)(col0 + c * 32), ragged, p.n_db, buf, count, thr, stash);
                     tc_ld_wait();
                     if (c + 2 < TC_N / 32) tc_ld32(taddr + (c + 2) * 32, va);
-                    tc_filter32<CAP>(vb, (uint32_t)(col0 + (c + 1) * 32), ragged, p.n_db, buf, count, thr);
+                    tc_filter32<CAP>(vb, (uint32_t)(col0 + (c + 1) * 32), ragged, p.n_db, buf, count, thr, stash);
                 }
                 tc_fence_before();
                 __syncwarp();
