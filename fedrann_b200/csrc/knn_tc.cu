@@ -35,11 +35,14 @@ namespace {
 constexpr int TC_M = 128;                        // query rows per tile (TMEM lanes)
 constexpr int TC_N = 256;                        // database rows per tile (TMEM columns)
 constexpr int TC_KB = 64;                        // K elements per smem block: 128 B = one swizzle row
-constexpr int TC_THREADS = 192;                  // warp 0 TMA, warp 1 MMA, warps 2-5 epilogue
+constexpr int TC_EPQ = 2;                        // epilogue warps per TMEM lane quadrant
+constexpr int TC_THREADS = 64 + 128 * TC_EPQ;    // warp 0 TMA, warp 1 MMA, then 4*TC_EPQ epilogue warps
+constexpr int TC_CH = 16;                        // columns per epilogue chunk (one tcgen05.ld.x16)
 constexpr int TC_ABLK = TC_M * TC_KB * 2;        // 16 KB per resident A block
-constexpr int TC_NS = 128;                       // database rows per B stage / per MMA
-constexpr int TC_STAGE = TC_NS * TC_KB * 2;      // 16 KB per B stage
-constexpr int TC_STASH = 4 * 32 * 32 * 4;        // 16 KB: one 32x32 fp32 chunk per epilogue warp
+constexpr int TC_NS = 256;                       // database rows per B stage / per MMA (N=128 MMAs are smem-bound)
+constexpr int TC_STAGE = TC_NS * TC_KB * 2;      // 32 KB per B stage
+constexpr int TC_STASH = 0;                      // (no shared-memory stash: hit columns are replayed from registers)
+constexpr int TC_ROWST = TC_M * 8;               // per-row threshold + append counter
 constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_MAX_KBLKS = 8;                  // Dp <= 512 keeps the query tile resident
 constexpr int TC_MAX_SLOTS = 6;
@@ -53,7 +56,7 @@ struct TcParams {
     int64_t n_db, nq, q0;
     int kblks, stages;
     int64_t db_tiles, q_tiles, units;
-    int n_ctas, slots, kprime;
+    int n_ctas, slots, klo, khi;
     unsigned long long *keys;
     int *counts;
     float *thrs;
@@ -222,56 +225,55 @@ __device__ __forceinline__ int tc_owner(int64_t u, int64_t units, int n_ctas) {
     return (int)(((u + 1) * n_ctas - 1) / units);
 }
 
-// Epilogue inner step: 32 scores of one query row (this thread's TMEM lane) against the row's
-// running threshold.  The chunk maximum is tested first; only when some lane of the warp has a
-// score above its threshold is the chunk stashed in shared memory (float4 per lane, conflict
-// free) and a per-lane hit mask built, after which every lane walks ITS OWN set bits -- the
-// warp's cost is the largest hit count among its lanes, not 32 predicated store sequences.
-// Survivors are appended to the row's candidate buffer; a buffer that could overflow during
-// the next 32 columns is compacted by the whole warp (tc_warp_select) and the threshold rises.
-template <int CAP>
-__device__ __forceinline__ void tc_filter32(const uint32_t (&v)[32], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *buf, int &count, float &thr, float4 *stash) {
+__device__ __forceinline__ void tc_quad_bar(int id) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(32 * TC_EPQ) : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+
+// Epilogue inner step: 16 scores of one query row (this thread's TMEM lane) against the row's
+// threshold.  The chunk maximum is tested first; only when some lane of the warp has a score
+// above its threshold does each lane build a 16-bit hit mask and walk its own set bits; the
+// warp's cost is the largest hit count among its lanes.  Append positions are reserved once
+// per chunk from a shared-memory counter (the warps of one TMEM lane quadrant share rows).
+__device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
+                                            unsigned long long *buf, int *cnt, float thr) {
     float m = -INFINITY;
 #pragma unroll
-    for (int g = 0; g < 8; ++g)
+    for (int g = 0; g < 4; ++g)
         m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
                            fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]))));
     if (__any_sync(0xFFFFFFFFu, m > thr)) {
         uint32_t mask = 0;
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-            stash[g * 32] = make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
-                                        __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                mask |= (__uint_as_float(v[4 * g + e]) > thr ? 1u : 0u) << (4 * g + e);
-        }
+        for (int j = 0; j < 16; ++j) mask |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
         if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
             const int64_t left = n_db - (int64_t)cbase;
-            mask = left >= 32 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
+            mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
         }
-        const float *sf = reinterpret_cast<const float *>(stash);
-        while (mask) {
-            const int j = __ffs(mask) - 1;
-            mask &= mask - 1;
-            const float f = sf[(j >> 2) * 128 + (j & 3)];     // own float4 slot g = j/4, element j%4
-            buf[count] = tc_key(f, cbase + j);
-            ++count;
+        if (mask) {
+            // one reservation per chunk, then this lane walks ITS OWN hits; the value is picked from
+            // the registers by a 4-level select tree on the bits of j (no dynamic register indexing)
+            int pos = atomicAdd(cnt, __popc(mask));
+            do {
+                const int j = __ffs(mask) - 1;
+                mask &= mask - 1;
+                uint32_t a8[8], a4[4];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a8[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) a4[i] = (j & 2) ? a8[2 * i + 1] : a8[2 * i];
+                const uint32_t b0 = (j & 4) ? a4[1] : a4[0], b1 = (j & 4) ? a4[3] : a4[2];
+                const uint32_t x = (j & 8) ? b1 : b0;
+                buf[pos++] = tc_key(__uint_as_float(x), cbase + j);
+            } while (mask);
         }
-    }
-    unsigned need = __ballot_sync(0xFFFFFFFFu, count > CAP - 32);
-    while (need) {
-        const int lane = threadIdx.x & 31;
-        const int src = __ffs(need) - 1;
-        need &= need - 1;
-        const int n = __shfl_sync(0xFFFFFFFFu, count, src);
-        const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
-        __syncwarp();
-        int kept;
-        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n, 3 * CAP / 8,
-                                                  5 * CAP / 8, &kept);
-        if (lane == src) { thr = nt; count = kept; }
     }
 }
 
@@ -286,7 +288,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     const uint32_t sA = base;
     const uint32_t sB = sA + p.kblks * TC_ABLK;
     const uint32_t sStash = sB + p.stages * TC_STAGE;
-    const uint32_t sBar = sStash + TC_STASH;
+    const uint32_t sRow = sStash + TC_STASH;
+    const uint32_t sBar = sRow + TC_ROWST;
     // barriers: full[8] empty[8] a_full a_empty tmem_full[2] tmem_empty[2], then the TMEM base address
     const uint32_t bFull = sBar, bEmpty = sBar + 64, bAFull = sBar + 128, bAEmpty = sBar + 136,
                    bTFull = sBar + 144, bTEmpty = sBar + 160;
@@ -297,7 +300,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(bFull + 8 * s, 1); mbar_init(bEmpty + 8 * s, 1); }
         mbar_init(bAFull, 1);
         mbar_init(bAEmpty, 1);
-        for (int b = 0; b < 2; ++b) { mbar_init(bTFull + 8 * b, 1); mbar_init(bTEmpty + 8 * b, 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(bTFull + 8 * b, 1); mbar_init(bTEmpty + 8 * b, 4 * TC_EPQ); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -313,7 +316,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
 
     const int cta = blockIdx.x;
     const bool dbg_on = p.dbg != nullptr;
-    long long w0 = 0, w1 = 0;
+    long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0;
     const long long t_start = clock64();
     const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
     const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
@@ -335,8 +338,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                         for (int h = 0; h < TC_N / TC_NS; ++h) {
                             mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
                             mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
-                            tma_load_2d(sB + stage * TC_STAGE, &tmap, bFull + 8 * stage, kb * TC_KB,
-                                        (int)(t * TC_N + h * TC_NS));
+                            for (int b = 0; b < TC_NS / TC_M; ++b)      // box = 64 x 128 rows
+                                tma_load_2d(sB + stage * TC_STAGE + b * TC_ABLK, &tmap, bFull + 8 * stage, kb * TC_KB,
+                                            (int)(t * TC_N + h * TC_NS + b * TC_M));
                             if (++stage == p.stages) { stage = 0; phase ^= 1; }
                         }
                     }
@@ -381,9 +385,15 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         }
     } else {
         // ------------------------------------------------ epilogue: threshold filter + candidate buffers
+        // TC_EPQ warps share each TMEM lane quadrant (32 query rows): they take alternate 16-column
+        // chunks of every tile, append through a shared-memory counter per row, and compact full
+        // buffers between tiles (rows split among the quadrant's warps).
         const int quad = warp & 3;                       // TMEM lanes 32*quad .. 32*quad+31
-        float4 *stash = reinterpret_cast<float4 *>(gbase + (sStash - base)) + quad * 256 + lane;
+        const int sub = (warp - 2) >> 2;                 // which of the quadrant's warps
         const int row_in_tile = quad * 32 + lane;
+        float *s_thr = reinterpret_cast<float *>(gbase + (sRow - base));
+        int *s_cnt = reinterpret_cast<int *>(s_thr + TC_M);
+        const int bar_id = 1 + quad;
         uint32_t tile = 0;
         for (int64_t u = u_begin; u < u_end;) {
             const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
@@ -393,31 +403,57 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
             const int64_t stream = (valid ? grow : 0) * p.slots + slot;
             unsigned long long *buf = p.keys + stream * CAP;
-            int count = 0;
-            float thr = valid ? -INFINITY : INFINITY;
+            if (sub == 0) { s_thr[row_in_tile] = valid ? -INFINITY : INFINITY; s_cnt[row_in_tile] = 0; }
+            tc_quad_bar(bar_id);
             for (int64_t t = t0; t < t1; ++t, ++tile) {
                 const uint32_t ab = tile & 1;
                 mbar_wait_t(bTFull + 8 * ab, (tile >> 1) & 1, w0, dbg_on);
                 tc_fence_after();
+                const float thr = s_thr[row_in_tile];
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
                 const int64_t col0 = t * TC_N;
                 const bool ragged = col0 + TC_N > p.n_db;
-                uint32_t va[32], vb[32];
-                tc_ld32(taddr, va);
+                uint32_t va[TC_CH], vb[TC_CH];
+                tc_ld16(taddr + sub * TC_CH, va);
 #pragma unroll 1
-                for (int c = 0; c < TC_N / 32; c += 2) {
-                    tc_ld_wait();                                   // va landed
-                    tc_ld32(taddr + (c + 1) * 32, vb);              // next chunk in flight while va is filtered
-                    tc_filter32<CAP>(va, (uint32_t)(col0 + c * 32), ragged, p.n_db, buf, count, thr, stash);
+                for (int c = sub; c < TC_N / TC_CH; c += 2 * TC_EPQ) {
+                    long long tq = dbg_on ? clock64() : 0;
+                    tc_ld_wait();                                          // va landed
+                    if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
+                    tc_ld16(taddr + (c + TC_EPQ) * TC_CH, vb);             // next own chunk in flight
+                    tc_filter16(va, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, buf, s_cnt + row_in_tile, thr);
+                    if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();
-                    if (c + 2 < TC_N / 32) tc_ld32(taddr + (c + 2) * 32, va);
-                    tc_filter32<CAP>(vb, (uint32_t)(col0 + (c + 1) * 32), ragged, p.n_db, buf, count, thr, stash);
+                    if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
+                    if (c + 2 * TC_EPQ < TC_N / TC_CH) tc_ld16(taddr + (c + 2 * TC_EPQ) * TC_CH, va);
+                    tc_filter16(vb, (uint32_t)(col0 + (c + TC_EPQ) * TC_CH), ragged, p.n_db, buf,
+                                s_cnt + row_in_tile, thr);
+                    if (dbg_on) e_flt += clock64() - tq;
                 }
+                long long tb = dbg_on ? clock64() : 0;
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
+                tc_quad_bar(bar_id);                     // every append of this tile is visible
+                if (dbg_on) { const long long t2 = clock64(); e_bar += t2 - tb; tb = t2; }
+                // a buffer that could overflow during the next tile is compacted now
+                unsigned need = __ballot_sync(0xFFFFFFFFu, s_cnt[row_in_tile] > CAP - TC_N);
+                while (need) {
+                    const int src = __ffs(need) - 1;
+                    need &= need - 1;
+                    if (src % TC_EPQ != sub) continue;   // the quadrant's other warp takes this row
+                    const int n = __shfl_sync(0xFFFFFFFFu, s_cnt[row_in_tile], src);
+                    const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
+                    int kept;
+                    const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n, p.klo,
+                                                              p.khi, &kept);
+                    if (lane == src) { s_thr[row_in_tile] = nt; s_cnt[row_in_tile] = kept; }
+                }
+                if (dbg_on) { const long long t2 = clock64(); e_cmp += t2 - tb; tb = t2; }
+                tc_quad_bar(bar_id);                     // new thresholds / counts are visible
+                if (dbg_on) e_bar += clock64() - tb;
             }
-            if (valid) { p.counts[stream] = count; p.thrs[stream] = thr; }
+            if (sub == 0 && valid) { p.counts[stream] = s_cnt[row_in_tile]; p.thrs[stream] = s_thr[row_in_tile]; }
             u += t1 - t0;
         }
     }
@@ -427,7 +463,11 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         const long long life = clock64() - t_start;
         if (warp == 0) atomicAdd(&p.dbg[0], (unsigned long long)w0);
         else if (warp == 1) { atomicAdd(&p.dbg[1], (unsigned long long)w0); atomicAdd(&p.dbg[2], (unsigned long long)w1); }
-        else { atomicAdd(&p.dbg[3], (unsigned long long)w0); atomicAdd(&p.dbg[4], (unsigned long long)(life - w0)); }
+        else {
+            atomicAdd(&p.dbg[3], (unsigned long long)w0); atomicAdd(&p.dbg[4], (unsigned long long)(life - w0));
+            atomicAdd(&p.dbg[8], (unsigned long long)e_ld); atomicAdd(&p.dbg[9], (unsigned long long)e_flt);
+            atomicAdd(&p.dbg[10], (unsigned long long)e_bar); atomicAdd(&p.dbg[11], (unsigned long long)e_cmp);
+        }
         if (warp == 0) atomicAdd(&p.dbg[5], (unsigned long long)life);
     }
     tc_fence_before();
@@ -628,12 +668,15 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
     EncodeTiledFn encode = get_encode_fn();
     if (!encode) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled is not available");
-    const int cap = k <= 32 ? 128 : (k <= 64 ? 256 : 512);
+    // selection window (how many candidates a compaction keeps) and the physical buffer size: a
+    // row may gain a whole tile (256 columns) between compactions
+    const int win = k <= 32 ? 128 : (k <= 64 ? 256 : 512);
+    const int cap = win <= 256 ? 512 : 1024;
 
     TcParams p{};
     p.n_db = n_db; p.nq = nq; p.q0 = q0;
     p.kblks = Dp / TC_KB;
-    const size_t fixed = 1024 + 256 + TC_STASH + (size_t)p.kblks * TC_ABLK;
+    const size_t fixed = 1024 + 256 + TC_STASH + TC_ROWST + (size_t)p.kblks * TC_ABLK;
     int stages = (int)((232448 - fixed) / TC_STAGE);
     p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
     const size_t smem = fixed + (size_t)p.stages * TC_STAGE;
@@ -651,7 +694,8 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
         if ((int)(b - a + 1) > p.slots) p.slots = (int)(b - a + 1);
     }
     if (p.slots > TC_MAX_SLOTS) return fr_fail(ctx, FR_ERR_STATE, "fr_knn: internal slot bound exceeded");
-    p.kprime = cap / 2;
+    p.klo = 3 * win / 8;
+    p.khi = 5 * win / 8;
     p.norms = d_norms;
 
     // workspace: keys | counts | thrs | fallback rows | fallback counter
@@ -672,8 +716,8 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     static const bool dbg_env = getenv("FR_KNN_DEBUG") != nullptr;
     static unsigned long long *d_dbg = nullptr;
     if (dbg_env) {
-        if (!d_dbg) cudaMalloc(&d_dbg, 64);
-        cudaMemsetAsync(d_dbg, 0, 64, st);
+        if (!d_dbg) cudaMalloc(&d_dbg, 128);
+        cudaMemsetAsync(d_dbg, 0, 128, st);
         p.dbg = d_dbg;
     }
     CUtensorMap tmap;
@@ -686,22 +730,23 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled failed");
 
-    if (cap == 128)
-        rc = tc_run<128>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
-    else if (cap == 256)
-        rc = tc_run<256>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
-    else
+    if (cap == 512)
         rc = tc_run<512>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
+    else
+        rc = tc_run<1024>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
     if (rc) return rc;
     if (dbg_env) {
-        unsigned long long h[8];
+        unsigned long long h[16];
         cudaStreamSynchronize(st);
-        cudaMemcpy(h, d_dbg, 64, cudaMemcpyDeviceToHost);
+        cudaMemcpy(h, d_dbg, 128, cudaMemcpyDeviceToHost);
         const double n = p.n_ctas;
         fprintf(stderr, "[fr_knn dbg] per-CTA Mcycles: life %.2f | producer wait-empty %.2f | mma wait-data %.2f wait-tmem %.2f"
-                        " | epilogue(avg of 4) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
-                h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / 4e6, h[4] / n / 4e6,
+                        " | epilogue(avg per warp) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
+                h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / (4e6 * TC_EPQ), h[4] / n / (4e6 * TC_EPQ),
                 (double)p.units / n);
+        const double ew = n * 4e6 * TC_EPQ;
+        fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f\n",
+                h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew);
     }
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
     rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, d_idx, d_dist, st);
