@@ -499,82 +499,92 @@ __device__ void rr_warp_sort(unsigned long long *a, int n_pow2) {
     }
 }
 
-template <int CAP>
+constexpr int RR_RES = 128;       // most candidates one row may re-rank exactly (k <= 128)
+
+// K7.  One warp per query row.
+//  1. merge the row's candidate buffers (approximate fp16-operand scores) into shared memory;
+//  2. find a score T with at least k (and at most k+8, unless ties forbid it) candidates >= T;
+//     those k candidates have exact similarity >= T - eps, so anything whose approximate score
+//     is below T - 2 eps cannot be among the exact top k.  That holds for every candidate the
+//     K6 epilogue dropped iff each buffer's final threshold is < T - 2 eps: the certificate;
+//  3. recompute the survivors (approximate score >= T - 2 eps; typically k + a few) in fp32 with
+//     the SAME summation order as fr_knn_exact_kernel, sort by (distance, index), emit the top k.
+// Rows that fail the certificate, or have more than RR_RES survivors, go to the exact scan.
 __global__ void __launch_bounds__(RR_WARPS * 32)
 fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
-                     int64_t nq, int k, int slots, const unsigned long long *__restrict__ keys,
+                     int64_t nq, int k, int slots, int cap, int max_n, const unsigned long long *__restrict__ keys,
                      const int *__restrict__ counts, const float *__restrict__ thrs, int32_t *__restrict__ out_idx,
                      float *__restrict__ out_dist, int32_t *__restrict__ fb_rows, unsigned long long *fb_count) {
-    constexpr int KEEP = CAP / 2;
     extern __shared__ __align__(16) unsigned char rr_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const size_t per_warp = (size_t)slots * CAP * 8 + (size_t)KEEP * 8 * 2;
+    const size_t per_warp = (size_t)max_n * 8 + (size_t)RR_RES * 8;
     unsigned long long *cand = reinterpret_cast<unsigned long long *>(rr_smem + warp * per_warp);
-    unsigned long long *res = cand + (size_t)slots * CAP;        // [KEEP] sorted (dist, idx) keys; power of two
+    unsigned long long *res = cand + max_n;                       // [RR_RES] (dist, idx) keys
     for (int64_t row = (int64_t)blockIdx.x * RR_WARPS + warp; row < nq; row += (int64_t)gridDim.x * RR_WARPS) {
         const float qn = norms[q0 + row];
         if (qn == 0.0f) {   // zero-norm query: distance 1 to everything, ties by lower index
             for (int j = lane; j < k; j += 32) { out_idx[row * k + j] = j; out_dist[row * k + j] = 1.0f; }
             continue;
         }
-        // ---- merge this row's candidate buffers
+        // ---- 1. merge this row's candidate buffers
         int n = 0;
-        float tau = -INFINITY;
+        float tau = -INFINITY;      // largest final threshold of a buffer that ever dropped something
+        bool ok = true;
         for (int s = 0; s < slots; ++s) {
             const int c = counts[row * slots + s];
             if (c == 0) continue;
             tau = fmaxf(tau, thrs[row * slots + s]);
-            const unsigned long long *src = keys + (row * slots + s) * CAP;
+            if (n + c > max_n) { ok = false; break; }
+            const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
             for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + i);
             n += c;
         }
         __syncwarp();
-        // ---- keep the KEEP best approximate scores (exact selection on the 64-bit keys)
-        int m = n;
-        if (n > KEEP) {
-            uint32_t T = 0;
-            for (int b = 31; b >= 0; --b) {
-                const uint32_t cd = T | (1u << b);
-                int c = 0;
-                for (int i = lane; i < n; i += 32) c += (uint32_t)(cand[i] >> 32) >= cd;
-                if (__reduce_add_sync(0xFFFFFFFFu, c) >= KEEP) T = cd;
-            }
-            int cgt = 0, ceq = 0;
-            for (int i = lane; i < n; i += 32) {
-                const uint32_t h = (uint32_t)(cand[i] >> 32);
-                cgt += h > T;
-                ceq += h == T;
-            }
-            cgt = __reduce_add_sync(0xFFFFFFFFu, cgt);
-            ceq = __reduce_add_sync(0xFFFFFFFFu, ceq);
-            const int need = KEEP - cgt;
-            uint32_t U = 0;
-            if (ceq > need) {
-                for (int b = 31; b >= 0; --b) {
-                    const uint32_t cd = U | (1u << b);
+        ok = ok && n >= k;
+        // ---- 2. T: between k and k+8 candidates score >= T (prefix skip + early exit, as in K6)
+        uint32_t T = 0;
+        if (ok) {
+            uint32_t mx = 0, mn = 0xFFFFFFFFu;
+            for (int i = lane; i < n; i += 32) { const uint32_t h = (uint32_t)(cand[i] >> 32); mx = max(mx, h); mn = min(mn, h); }
+            mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+            mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+            T = mn;
+            if (n > k + 8 && mx != mn) {
+                const int b0 = 31 - __clz(mx ^ mn);
+                T = b0 == 31 ? 0u : (mx >> (b0 + 1)) << (b0 + 1);
+                for (int b = b0; b >= 0; --b) {
+                    const uint32_t cd = T | (1u << b);
                     int c = 0;
-                    for (int i = lane; i < n; i += 32)
-                        c += ((uint32_t)(cand[i] >> 32) == T) && ((uint32_t)cand[i] >= cd);
-                    if (__reduce_add_sync(0xFFFFFFFFu, c) >= need) U = cd;
+                    for (int i = lane; i < n; i += 32) c += (uint32_t)(cand[i] >> 32) >= cd;
+                    c = __reduce_add_sync(0xFFFFFFFFu, c);
+                    if (c >= k) { T = cd; if (c <= k + 8) break; }
                 }
             }
-            // compact in place, front to back (a write never passes the read position)
-            int pos = 0;
+        }
+        // ---- survivors: approximate score >= T - 2 eps, compacted to the front of cand
+        int m = 0;
+        float cut = -INFINITY;
+        if (ok) {
+            cut = ord2f(T) - 2.0f * TC_EPS;
+            const uint32_t Lo = f2ord(cut);
             for (int i0 = 0; i0 < n; i0 += 32) {
                 const int i = i0 + lane;
-                unsigned long long key = i < n ? cand[i] : 0ull;
-                const uint32_t h = (uint32_t)(key >> 32), l = (uint32_t)key;
-                const bool kp = i < n && (h > T || (h == T && l >= U));
+                const unsigned long long key = i < n ? cand[i] : 0ull;
+                const bool kp = i < n && (uint32_t)(key >> 32) >= Lo;
                 const unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
                 __syncwarp();
-                if (kp) cand[pos + __popc(bal & ((1u << lane) - 1))] = key;
-                pos += __popc(bal);
+                if (kp) cand[m + __popc(bal & ((1u << lane) - 1))] = key;   // never passes the read position
+                m += __popc(bal);
                 __syncwarp();
             }
-            m = pos;
-            tau = fmaxf(tau, ord2f(T));
+            // certificate: every buffer's dropped candidates scored <= its threshold < T - 2 eps
+            ok = m <= RR_RES && (tau == -INFINITY || tau < cut);
         }
-        // ---- exact fp32 similarities, same summation order as fr_knn_exact_kernel
+        if (!ok) {
+            if (lane == 0) fb_rows[atomicAdd(fb_count, 1ull)] = (int32_t)row;
+            continue;
+        }
+        // ---- 3. exact fp32 similarities, same summation order as fr_knn_exact_kernel
         float q[16];
         const float *qp = En + (q0 + row) * D;
 #pragma unroll
@@ -594,7 +604,7 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-                for (int s = 16; s > 0; s >>= 1) acc[u] += __shfl_xor_sync(0xFFFFFFFFu, acc[u], s);
+                for (int sh = 16; sh > 0; sh >>= 1) acc[u] += __shfl_xor_sync(0xFFFFFFFFu, acc[u], sh);
             if (lane < 4 && c0 + lane < m) {
                 const float a = lane == 0 ? acc[0] : lane == 1 ? acc[1] : lane == 2 ? acc[2] : acc[3];
                 const uint32_t ii = lane == 0 ? id[0] : lane == 1 ? id[1] : lane == 2 ? id[2] : id[3];
@@ -602,22 +612,15 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
                 res[c0 + lane] = ((unsigned long long)f2ord(d) << 32) | ii;   // ascending (dist, idx)
             }
         }
-        for (int i = m + lane; i < KEEP; i += 32) res[i] = 0xFFFFFFFFFFFFFFFFull;
+        int mp = 32;
+        while (mp < m) mp <<= 1;
+        for (int i = m + lane; i < mp; i += 32) res[i] = 0xFFFFFFFFFFFFFFFFull;
         __syncwarp();
-        rr_warp_sort(res, KEEP);
+        rr_warp_sort(res, mp);
         for (int j = lane; j < k; j += 32) {
             const unsigned long long key = res[j];
-            out_idx[row * k + j] = j < m ? (int32_t)(uint32_t)key : -1;
-            out_dist[row * k + j] = j < m ? ord2f((uint32_t)(key >> 32)) : INFINITY;
-        }
-        // ---- certification: nothing dropped can beat the k-th exact neighbour
-        if (lane == 0) {
-            bool ok = m >= k;
-            if (ok && tau > -INFINITY) {
-                const float dk = ord2f((uint32_t)(res[k - 1] >> 32));
-                ok = dk < 1.0f - (tau + TC_EPS);
-            }
-            if (!ok) fb_rows[atomicAdd(fb_count, 1ull)] = (int32_t)row;
+            out_idx[row * k + j] = (int32_t)(uint32_t)key;
+            out_dist[row * k + j] = ord2f((uint32_t)(key >> 32));
         }
         __syncwarp();
     }
@@ -647,14 +650,16 @@ int tc_run(fr_ctx *ctx, const CUtensorMap &tmap, const TcParams &p, size_t smem,
     fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
     fr_knn_tc_kernel<CAP><<<p.n_ctas, TC_THREADS, smem, st>>>(tmap, p);
     FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
-    const size_t rsmem = (size_t)RR_WARPS * ((size_t)p.slots * CAP * 8 + (size_t)(CAP / 2) * 16);
-    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)rsmem));
+    int max_n = p.slots * CAP;                         // keys one row can hold across its buffers
+    if (max_n > 4096) max_n = 4096;                    // (rows beyond it go to the exact scan)
+    const size_t rsmem = (size_t)RR_WARPS * ((size_t)max_n * 8 + (size_t)RR_RES * 8);
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
     int64_t blocks = (p.nq + RR_WARPS - 1) / RR_WARPS;
     if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
     fr_kt_begin(ctx, "fr_knn_rerank_kernel", st);
-    fr_knn_rerank_kernel<CAP><<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
-        d_En, d_norms, p.n_db, D, p.q0, p.nq, k, p.slots, p.keys, p.counts, p.thrs, d_idx, d_dist, fb_rows, fb_count);
+    fr_knn_rerank_kernel<<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
+        d_En, d_norms, p.n_db, D, p.q0, p.nq, k, p.slots, CAP, max_n, p.keys, p.counts, p.thrs, d_idx, d_dist, fb_rows,
+        fb_count);
     FR_LAUNCH_CHECK(ctx, "fr_knn_rerank_kernel");
     return FR_OK;
 }
