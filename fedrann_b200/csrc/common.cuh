@@ -12,14 +12,13 @@
 #define FR_HASH_MUL 0x9E3779B97F4A7C15ull
 
 // Device-side view of the k-mer lookup structure (K2 builds it, K3 probes it).
-//  * bloom: blocked Bloom filter, one 32-bit block per probe (1 L2 sector),
-//    3 bits per key, sized 16-32 bits per key so it stays L2-resident.
-//  * keys/vals: open-addressing table (linear probing, <= 50 % load), only
-//    touched by the few percent of probes that pass the filter.
+//  * bloom: one-bit-per-key filter, 32-64 bits per key (a false-positive rate of 1.5-3 %), small
+//    enough to stay L2-resident; a probe is ONE 32-byte L2 sector and ~5 instructions.
+//  * slots: open-addressing table of 16-byte slots {key lo, key hi, value, pad} (linear
+//    probing, <= 70 % load) so that a probe that passes the filter costs one sector, too.
 struct FrTable {
     const uint32_t *bloom;
-    const uint64_t *keys;
-    const uint32_t *vals;
+    const uint4 *slots;
     int lg_words;  // log2(#bloom words)
     int lg_cap;    // log2(#table slots)
     int k;
@@ -34,8 +33,7 @@ struct fr_ctx {
 
     // K2
     uint32_t *d_bloom = nullptr;
-    uint64_t *d_keys = nullptr;
-    uint32_t *d_vals = nullptr;
+    uint4 *d_slots = nullptr;
     FrTable table{};
     bool has_table = false;
 
@@ -61,6 +59,12 @@ struct fr_ctx {
     bool kt_open = false;
     cudaStream_t kt_stream = nullptr;
     std::vector<KtRec> kt;
+
+    // N1 k-mer count table
+    uint4 *d_count_slots = nullptr;
+    int64_t count_cap_bytes = 0;
+    int count_lg_cap = 0;
+    int count_k = 0;
 
     // K6/K7 scratch
     void *d_knn_ws = nullptr;
@@ -94,16 +98,19 @@ void fr_kt_end(fr_ctx *ctx);
 __device__ __forceinline__ uint64_t fr_hash(uint64_t kmer) {
     return (kmer ^ (kmer >> 29)) * FR_HASH_MUL;
 }
-__device__ __forceinline__ uint32_t fr_bloom_word(uint64_t h, int lg_words) {
-    return (uint32_t)(h >> (64 - lg_words));
-}
-__device__ __forceinline__ uint32_t fr_bloom_mask(uint64_t h) {
-    uint32_t lo = (uint32_t)h;
-    return (1u << (lo >> 27)) | (1u << ((lo >> 22) & 31)) | (1u << ((lo >> 17) & 31));
-}
 __device__ __forceinline__ uint32_t fr_table_slot(uint64_t h, int lg_cap) {
     return (uint32_t)(h >> (64 - lg_cap));
 }
+// Filter hash: 32-bit multiplicative.  k-mers of k <= 16 fit one word (hi == 0).
+#define FR_BLOOM_MUL1 0x9E3779B1u
+#define FR_BLOOM_MUL2 0x85EBCA77u
+__device__ __forceinline__ uint32_t fr_bloom_hash(uint32_t lo, uint32_t hi) {
+    return lo * FR_BLOOM_MUL1 + hi * FR_BLOOM_MUL2;
+}
+// word index = top lg_words bits; the tested bit is 31 - (the next 5 bits), so that the probe
+// is `word << x` followed by a sign-bit test (x = h >> (27 - lg_words), shift taken mod 32)
+__device__ __forceinline__ uint32_t fr_bloom_word(uint32_t h, int lg_words) { return h >> (32 - lg_words); }
+__device__ __forceinline__ uint32_t fr_bloom_shift(uint32_t h, int lg_words) { return (h >> (27 - lg_words)) & 31u; }
 
 // internal launchers (defined in the .cu files)
 int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,

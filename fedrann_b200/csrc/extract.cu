@@ -5,39 +5,50 @@
 //
 // One CTA per read.  The read is walked in tiles of FR_TILE positions:
 //   K1  the tile's ASCII is loaded with 16-byte vector loads and packed to
-//       2-bit codes + a 1-bit "non-ACGT" mask in shared memory;
-//   K3a every thread rolls the reference's k-mer register over 32 consecutive
-//       positions (replaying the reference's state machine exactly, including
-//       the UINT64_MAX quirk), tests each k-mer against the blocked Bloom
-//       filter (one 32-byte L2 sector per probe) and queues the few survivors;
-//   K3b the queue is drained against the open-addressing table by full warps
-//       (no divergence on the rare hit path); hits go to a per-read list;
-//   K3c at the end of the read the list is sorted, de-duplicated and written
-//       to a bump-allocated scratch row; document frequencies are counted.
+//       2-bit codes (first base in the most significant bits, so that a k-mer
+//       is a funnel shift of two packed words) + a 1-bit "non-ACGT" mask;
+//   K3a every thread owns 32 consecutive positions; their k-mers are cut out of
+//       the packed words in registers (no loop-carried roll), hashed with one
+//       32-bit multiply and tested against the one-bit filter (one 32-byte L2
+//       sector per probe; the 32 probes of a thread are independent loads).
+//       The result is a 32-bit pass mask per thread; the tile positions of the
+//       survivors are queued in shared memory.  Positions whose window holds a
+//       non-ACGT base skip the filter and are queued unconditionally;
+//   K3b the queue is drained against the open-addressing table: the k-mer is
+//       rebuilt from the packed tile with the reference's exact semantics
+//       (UINT64_MAX quirk: bases at or before the last non-ACGT base of the
+//       window read as T; reads shorter than k are left-padded with A);
+//   K3c at the end of the read the hit list is sorted and de-duplicated: a
+//       counting pass splits it into value-range buckets of <= 128 entries and
+//       every warp sorts whole buckets in registers (shuffle bitonic network) --
+//       no block barrier inside the sort.  The row goes to a bump-allocated
+//       scratch CSR.
 #include "common.cuh"
+
+#include <cstdlib>
 
 #define FR_THREADS 256
 #define FR_PPT 32                       // positions per thread per tile
 #define FR_TILE (FR_THREADS * FR_PPT)   // 8192 positions
-#define FR_ROUNDS 4
-#define FR_PPR (FR_PPT / FR_ROUNDS)     // positions per thread per round
-#define FR_QCAP 4096                    // candidate queue (k-mers)
+#define FR_QCAP FR_TILE                 // candidate queue (tile positions): a tile can never overflow it
 #define FR_HCAP 4096                    // shared-memory hit list
 #define FR_NWORDS (FR_TILE / 16 + 2)    // packed words incl. 32 positions of look-behind
+#define FR_MAXB 64                      // most sort buckets (FR_HCAP / 64)
+#define FR_BCAP 128                     // entries one warp sorts in registers
 
 #define FR_FLAG_SCRATCH_OVERFLOW 1ull
 #define FR_FLAG_SPILL_OVERFLOW 2ull
 
-// ---- K1: 16 ASCII bytes -> 32 bits of codes + 16 invalid bits ----
+// ---- K1: 16 ASCII bytes -> 32 bits of codes + 16 invalid bits, first base most significant ----
 // code = ((b>>1)^(b>>2))&3 maps A/a 0, C/c 1, G/g 2, T/t 3 (kmer_searcher.cpp:316-322)
 __device__ __forceinline__ void fr_pack4(uint32_t w, uint32_t &codes8, uint32_t &inv4) {
     uint32_t t = ((w >> 1) ^ (w >> 2)) & 0x03030303u;
-    codes8 = (t | (t >> 6) | (t >> 12) | (t >> 18)) & 0xFFu;
+    codes8 = ((t << 6) | (t >> 4) | (t >> 14) | (t >> 24)) & 0xFFu;
     uint32_t x = w & 0xDFDFDFDFu;  // fold case
     uint32_t ok = __vcmpeq4(x, 0x41414141u) | __vcmpeq4(x, 0x43434343u) |
                   __vcmpeq4(x, 0x47474747u) | __vcmpeq4(x, 0x54545454u);
     uint32_t bad = ~ok;
-    inv4 = (bad & 1u) | ((bad >> 7) & 2u) | ((bad >> 14) & 4u) | ((bad >> 21) & 8u);
+    inv4 = ((bad << 3) & 8u) | ((bad >> 6) & 4u) | ((bad >> 15) & 2u) | ((bad >> 24) & 1u);
 }
 
 __device__ __forceinline__ void fr_pack16(uint4 v, uint32_t &codes, uint32_t &inv) {
@@ -46,11 +57,12 @@ __device__ __forceinline__ void fr_pack16(uint4 v, uint32_t &codes, uint32_t &in
     fr_pack4(v.y, c1, i1);
     fr_pack4(v.z, c2, i2);
     fr_pack4(v.w, c3, i3);
-    codes = c0 | (c1 << 8) | (c2 << 16) | (c3 << 24);
-    inv = i0 | (i1 << 4) | (i2 << 8) | (i3 << 12);
+    codes = (c0 << 24) | (c1 << 16) | (c2 << 8) | c3;
+    inv = (i0 << 12) | (i1 << 8) | (i2 << 4) | i3;
 }
 
 // ---- block-wide bitonic sort of n u32 (n padded with 0xFFFFFFFF to a power of two) ----
+// (general path: hit lists that spilled to global memory, mid-read compactions, skewed buckets)
 __device__ void fr_block_sort(uint32_t *a, int n_pow2) {
     for (int k = 2; k <= n_pow2; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -105,15 +117,145 @@ __device__ int fr_block_sort_unique(uint32_t *a, int n, int *s_scan /*[FR_THREAD
 }
 
 struct FrExtractShared {
-    uint64_t queue[FR_QCAP];
     uint32_t hits[FR_HCAP];
+    uint32_t tmp[FR_HCAP];      // K3c: hits grouped by bucket
     uint32_t codes[FR_NWORDS];
     uint32_t inv[FR_NWORDS];
+    uint16_t queue[FR_QCAP];
+    int bcnt[FR_MAXB + 1];      // K3c: bucket sizes -> unique counts
+    int bstart[FR_MAXB + 1];
+    int bfill[FR_MAXB + 1];     // scatter cursors -> output offsets
     int scan[FR_THREADS / 32 + 2];
-    int qcount;
     int hcount;
+    int flag;
     long long misc;
 };
+
+// ---- K3c fast path: sort + unique of sh.hits[0..n), n <= FR_HCAP ----
+// 128 values per warp, 4 per lane (element e = 4*lane + r), ascending.
+__device__ __forceinline__ void fr_warp_sort128(uint32_t (&v)[4], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 128; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= 4) {
+                const int lj = j >> 2;
+                const bool up = ((lane << 2) & k) == 0;
+                const bool lower = (lane & lj) == 0;
+                const bool keepmin = up == lower;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, v[r], lj);
+                    v[r] = keepmin ? min(v[r], o) : max(v[r], o);
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int r2 = r ^ j;
+                    if (r2 > r) {
+                        const bool up = (((lane << 2) | r) & k) == 0;
+                        const uint32_t a = v[r], b = v[r2];
+                        const uint32_t mn = min(a, b), mx = max(a, b);
+                        v[r] = up ? mn : mx;
+                        v[r2] = up ? mx : mn;
+                    }
+                }
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ int fr_warp_excl_scan(int x, int lane, int &total) {
+    int incl = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int y = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    return incl - x;
+}
+
+// Returns the unique count, or -1 when a bucket is too large (caller takes the general path;
+// sh.hits is untouched in that case).
+__device__ int fr_bucket_sort_unique(FrExtractShared &sh, int n, uint32_t n_features) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int lgB = 0;
+    while ((64 << lgB) < n) ++lgB;                                  // <= 64 entries per bucket on average
+    while (lgB > 0 && (n_features >> lgB) == 0) --lgB;
+    const int B = 1 << lgB;
+    // bucket = floor(v * B / F) (approximately; only monotonicity and b < B matter)
+    const unsigned long long m64 = ((0x100000000ull / n_features) << lgB);
+    const uint32_t M = m64 > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)m64;
+    if (tid <= B) sh.bcnt[tid] = 0;
+    if (tid == 0) sh.flag = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += FR_THREADS) atomicAdd(&sh.bcnt[__umulhi(sh.hits[i], M)], 1);
+    __syncthreads();
+    if (warp == 0) {
+        int carry = 0;
+        for (int b0 = 0; b0 < B; b0 += 32) {
+            const int c = b0 + lane < B ? sh.bcnt[b0 + lane] : 0;
+            int tot;
+            const int ex = fr_warp_excl_scan(c, lane, tot);
+            if (b0 + lane < B) { sh.bstart[b0 + lane] = carry + ex; sh.bfill[b0 + lane] = carry + ex; }
+            if (c > FR_BCAP) sh.flag = 1;
+            carry += tot;
+        }
+        if (lane == 0) sh.bstart[B] = carry;
+    }
+    __syncthreads();
+    if (sh.flag) return -1;
+    for (int i = tid; i < n; i += FR_THREADS) {
+        const uint32_t v = sh.hits[i];
+        sh.tmp[atomicAdd(&sh.bfill[__umulhi(v, M)], 1)] = v;
+    }
+    __syncthreads();
+    for (int b = warp; b < B; b += FR_THREADS / 32) {
+        const int a = sh.bstart[b], cnt = sh.bstart[b + 1] - a;
+        uint32_t v[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) v[r] = 4 * lane + r < cnt ? sh.tmp[a + 4 * lane + r] : 0xFFFFFFFFu;
+        fr_warp_sort128(v, lane);
+        uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, v[3], 1);
+        int c = 0;
+        bool keep[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int e = 4 * lane + r;
+            keep[r] = e < cnt && (e == 0 || v[r] != prev);
+            c += keep[r];
+            prev = v[r];
+        }
+        int tot;
+        int o = a + fr_warp_excl_scan(c, lane, tot);
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            if (keep[r]) sh.tmp[o++] = v[r];
+        if (lane == 0) sh.bcnt[b] = tot;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        int carry = 0;
+        for (int b0 = 0; b0 < B; b0 += 32) {
+            const int c = b0 + lane < B ? sh.bcnt[b0 + lane] : 0;
+            int tot;
+            const int ex = fr_warp_excl_scan(c, lane, tot);
+            if (b0 + lane < B) sh.bfill[b0 + lane] = carry + ex;
+            carry += tot;
+        }
+        if (lane == 0) sh.bfill[B] = carry;
+    }
+    __syncthreads();
+    for (int b = warp; b < B; b += FR_THREADS / 32) {
+        const int a = sh.bstart[b], o = sh.bfill[b], c = sh.bcnt[b];
+        for (int i = lane; i < c; i += 32) sh.hits[o + i] = sh.tmp[a + i];
+    }
+    const int u = sh.bfill[B];
+    __syncthreads();
+    return u;
+}
 
 struct FrHitList {
     uint32_t *ptr;  // shared memory first, a global spill slab for very long reads
@@ -121,69 +263,123 @@ struct FrHitList {
     bool dead;      // spill pool exhausted: the host grows it and reruns
 };
 
-// K3b: drain the candidate queue against the open-addressing table.
-__device__ void fr_flush(FrExtractShared &sh, FrHitList &hl, const FrTable &tb, int64_t n_lookups,
-                         uint32_t *spill, int64_t spill_cap, unsigned long long *counters) {
-    const int n = sh.qcount;
-    int hc = sh.hcount;
-    __syncthreads();  // everyone has read the counters before anyone moves them
-    if (n == 0) return;
-    if (hc + n > hl.cap && !hl.dead) {
-        int u = fr_block_sort_unique(hl.ptr, hc, sh.scan);
-        if (threadIdx.x == 0) sh.hcount = u;
-        __syncthreads();
-        hc = u;
-        if (hc + n > hl.cap) {
-            // migrate to a global slab that can hold one entry per lookup position
-            long long need = 1;
-            while (need < n_lookups) need <<= 1;
-            if (threadIdx.x == 0) sh.misc = (long long)atomicAdd(&counters[1], (unsigned long long)need);
-            __syncthreads();
-            long long off = sh.misc;
-            if (off + need > spill_cap) {
-                if (threadIdx.x == 0) atomicOr(&counters[2], FR_FLAG_SPILL_OVERFLOW);
-                hl.dead = true;
-            } else {
-                uint32_t *dst = spill + off;
-                for (int i = threadIdx.x; i < hc; i += FR_THREADS) dst[i] = hl.ptr[i];
-                hl.ptr = dst;
-                hl.cap = (int)(need > 0x40000000ll ? 0x40000000ll : need);
-            }
-            __syncthreads();
-        }
+// The k-mer the reference looks up at tile position `pos` (kmer_searcher.cpp:314-349), rebuilt
+// from the packed tile.  Returns false when the base at `pos` is not ACGT (no lookup, :325/:343).
+__device__ __forceinline__ bool fr_kmer_at(const FrExtractShared &sh, int pos, int K, uint64_t kmask,
+                                            uint64_t &kmer) {
+    const int u = pos + 32, W = u >> 4, r = u & 15;
+    const uint32_t w2 = sh.codes[W], w1 = sh.codes[W - 1], w0 = sh.codes[W - 2];
+    const int shc = 30 - 2 * r;
+    const uint32_t lo = __funnelshift_r(w2, w1, shc), hi = __funnelshift_r(w1, w0, shc);
+    kmer = (((uint64_t)hi << 32) | lo) & kmask;
+    const uint64_t iv = (((uint64_t)sh.inv[W - 2] << 32) | ((uint64_t)sh.inv[W - 1] << 16) | sh.inv[W]) >> (15 - r);
+    const uint32_t ivw = (uint32_t)iv & (uint32_t)((1ull << K) - 1);   // bit d = base pos - d
+    if (ivw & 1u) return false;
+    if (ivw) {
+        const int d = __ffs(ivw) - 1;                 // last non-ACGT base of the window is d bases back:
+        kmer = (kmer | ~((1ull << (2 * d)) - 1)) & kmask;   // it and everything before it read as T
     }
-    const uint32_t cap_mask = (uint32_t)((1ull << tb.lg_cap) - 1);
-    for (int i = threadIdx.x; i < n; i += FR_THREADS) {
-        uint64_t kmer = sh.queue[i];
-        uint32_t slot = fr_table_slot(fr_hash(kmer), tb.lg_cap);
-        while (true) {
-            uint64_t key = __ldg(&tb.keys[slot]);
-            if (key == kmer) {
-                uint32_t idx = __ldg(&tb.vals[slot]);
-                if (!hl.dead) {
-                    int pos = atomicAdd(&sh.hcount, 1);
-                    hl.ptr[pos] = idx;
-                }
-                break;
-            }
-            if (key == FR_EMPTY_KEY) break;
-            slot = (slot + 1) & cap_mask;
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) sh.qcount = 0;
-    __syncthreads();
+    return true;
 }
 
+// append one hit to the read's list; a full list raises sh.flag (the tile is redone after making room)
+__device__ __forceinline__ void fr_append_hit(FrExtractShared &sh, const FrHitList &hl, uint32_t idx) {
+    if (hl.dead) return;
+    const int pos = atomicAdd(&sh.hcount, 1);
+    if (pos < hl.cap) hl.ptr[pos] = idx;
+    else sh.flag = 1;
+}
+
+__device__ __forceinline__ void fr_probe_table(const FrTable &tb, uint64_t kmer, FrExtractShared &sh,
+                                               const FrHitList &hl) {
+    const uint32_t cap_mask = (uint32_t)((1ull << tb.lg_cap) - 1);
+    uint32_t slot = fr_table_slot(fr_hash(kmer), tb.lg_cap);
+    while (true) {
+        const uint4 v = __ldg(&tb.slots[slot]);
+        const uint64_t key = ((uint64_t)v.y << 32) | v.x;
+        if (key == kmer) { fr_append_hit(sh, hl, v.z); return; }
+        if (key == FR_EMPTY_KEY) return;
+        slot = (slot + 1) & cap_mask;
+    }
+}
+
+// K3b: one warp drains its own survivors (tile positions wq[0..n)) against the table.  The
+// first slot of FR_NB candidates per lane is requested before any is examined: a probe is a
+// random DRAM/L2 access and only the number of them in flight matters.
+#define FR_NB 4
+__device__ __forceinline__ void fr_warp_drain(FrExtractShared &sh, const FrHitList &hl, const FrTable &tb,
+                                              const uint16_t *wq, int n, int lane, uint64_t kmask) {
+    const uint32_t cap_mask = (uint32_t)((1ull << tb.lg_cap) - 1);
+    for (int i0 = 0; i0 < n; i0 += 32 * FR_NB) {
+        uint64_t km[FR_NB];
+        uint32_t slot[FR_NB];
+        uint4 v[FR_NB];
+        bool ok[FR_NB];
+#pragma unroll
+        for (int b = 0; b < FR_NB; ++b) {
+            const int i = i0 + 32 * b + lane;
+            km[b] = 0;
+            ok[b] = i < n && fr_kmer_at(sh, wq[i], tb.k, kmask, km[b]);
+            slot[b] = fr_table_slot(fr_hash(km[b]), tb.lg_cap);
+        }
+#pragma unroll
+        for (int b = 0; b < FR_NB; ++b) v[b] = ok[b] ? __ldg(&tb.slots[slot[b]]) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int b = 0; b < FR_NB; ++b) {
+            if (!ok[b]) continue;
+            uint4 w = v[b];
+            uint32_t sl = slot[b];
+            while (true) {
+                const uint64_t key = ((uint64_t)w.y << 32) | w.x;
+                if (key == km[b]) { fr_append_hit(sh, hl, w.z); break; }
+                if (key == FR_EMPTY_KEY) break;
+                sl = (sl + 1) & cap_mask;
+                w = __ldg(&tb.slots[sl]);
+            }
+        }
+    }
+}
+
+// K3a for one thread: 32 filter probes, all independent.  c0..c3 = packed codes of the 32
+// look-behind positions (c0, c1) and of the thread's own 32 positions (c2, c3).
+template <bool WIDE>
+__device__ __forceinline__ uint32_t fr_filter32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t kmask_lo,
+                                                uint32_t kmask_hi, const uint32_t *__restrict__ bloom, int wsh,
+                                                int bsh) {
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const int s = 62 - 2 * j;   // the k-mer ending at position j is (c0:c1:c2:c3) >> s
+        uint32_t lo, hi = 0;
+        if (s >= 32) {
+            lo = __funnelshift_r(c2, c1, s - 32);
+            if (WIDE) hi = __funnelshift_r(c1, c0, s - 32);
+        } else {
+            lo = __funnelshift_r(c3, c2, s);
+            if (WIDE) hi = __funnelshift_r(c2, c1, s);
+        }
+        uint32_t h;
+        if (WIDE) h = fr_bloom_hash(lo, hi & kmask_hi);
+        else h = (lo & kmask_lo) * FR_BLOOM_MUL1;
+        const uint32_t word = __ldg(bloom + (h >> wsh));
+        const uint32_t t = __funnelshift_l(0u, word, h >> bsh);   // word << ((h >> bsh) & 31): tested bit -> sign
+        pass = __funnelshift_l(t, pass, 1);                       // (pass << 1) | (t >> 31)
+    }
+    return pass;
+}
+
+template <bool WIDE>
 __global__ void __launch_bounds__(FR_THREADS, 4)
 fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int64_t *__restrict__ offsets,
                   int64_t n_reads, FrTable tb, int32_t *scratch, int64_t scratch_cap, uint32_t *spill,
-                  int64_t spill_cap, int64_t *read_off, int32_t *read_cnt, unsigned long long *counters) {
+                  int64_t spill_cap, int64_t *read_off, int32_t *read_cnt, unsigned long long *counters, int dbg) {
     extern __shared__ __align__(16) unsigned char fr_extract_smem[];
     FrExtractShared &sh = *reinterpret_cast<FrExtractShared *>(fr_extract_smem);
     const int tid = threadIdx.x, lane = tid & 31;
     const int K = tb.k;
     const uint64_t kmask = (1ull << (2 * K)) - 1;
+    const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
+    const int wsh = 32 - tb.lg_words, bsh = 27 - tb.lg_words;
     for (int64_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
         const int64_t s = offsets[r], e = offsets[r + 1];
         const int64_t len = e - s;
@@ -191,21 +387,21 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
         const int64_t lo = len >= K ? s + K - 1 : e - 1;  // first lookup position
         FrHitList hl;
         hl.ptr = sh.hits; hl.cap = FR_HCAP; hl.dead = false;
-        if (tid == 0) {
-            sh.hcount = 0;
-            sh.qcount = 0;
-            if (len == 0) { sh.queue[0] = 0; sh.qcount = 1; }  // kmer_searcher.cpp:325 with an empty read
-        }
+        if (tid == 0) { sh.hcount = 0; sh.flag = 0; }
         __syncthreads();
+        if (len == 0 && tid == 0) fr_probe_table(tb, 0ull, sh, hl);   // kmer_searcher.cpp:325 with an empty read
         const int64_t abase = s & ~15ll;
         const int64_t ntiles = len > 0 ? (e - abase + FR_TILE - 1) / FR_TILE : 0;
+        bool compacted = false;     // this tile was already retried after a compaction
         for (int64_t tile = 0; tile < ntiles; ++tile) {
             const int64_t tile_start = abase + tile * FR_TILE;
-            // ---- K1: pack this tile (plus 32 positions of look-behind) ----
+            const int hc0 = sh.hcount;      // uniform: a barrier precedes every iteration
+            // ---- K1: pack this tile (plus 32 positions of look-behind); bases outside the read are A, valid ----
             for (int w = tid; w < FR_NWORDS; w += FR_THREADS) {
                 const int64_t g = tile_start - 32 + 16ll * w;
-                uint4 v = make_uint4(0, 0, 0, 0);
+                uint32_t c = 0, iv = 0;
                 if (g + 16 > s && g < e) {
+                    uint4 v;
                     if (g >= 0 && g + 16 <= n_bases) {
                         v = __ldg(reinterpret_cast<const uint4 *>(bases + g));
                     } else {
@@ -216,69 +412,89 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                         }
                         v = make_uint4(b[0], b[1], b[2], b[3]);
                     }
+                    fr_pack16(v, c, iv);
+                    if (g < s) {            // 1..15 leading positions belong to the previous read
+                        const int nb = (int)(s - g);
+                        c &= 0xFFFFFFFFu >> (2 * nb);
+                        iv &= 0xFFFFu >> nb;
+                    }
                 }
-                uint32_t c, iv;
-                fr_pack16(v, c, iv);
                 sh.codes[w] = c;
                 sh.inv[w] = iv;
             }
             __syncthreads();
-            // ---- K3a: roll + filter ----
+            // ---- K3a: filter (warps run on their own from here to the end of the tile) ----
             const int64_t cstart = tile_start + (int64_t)FR_PPT * tid;
-            const bool active = cstart < e && cstart + FR_PPT > lo;
-            const bool warp_active = __any_sync(0xFFFFFFFFu, active);
-            uint64_t cur = 0, cw = 0;
-            uint32_t ivw = 0;
-            if (active) {
+            const int64_t jl = lo > cstart ? lo - cstart : 0, jh = e - cstart < FR_PPT ? e - cstart : FR_PPT;
+            uint32_t pass = 0;
+            if (jl < jh) {
                 const int wi = 2 * tid;
-                uint64_t cww = (uint64_t)sh.codes[wi] | ((uint64_t)sh.codes[wi + 1] << 32);
-                uint32_t ivv = sh.inv[wi] | (sh.inv[wi + 1] << 16);
-                cw = (uint64_t)sh.codes[wi + 2] | ((uint64_t)sh.codes[wi + 3] << 32);
-                ivw = sh.inv[wi + 2] | (sh.inv[wi + 3] << 16);
-                const int64_t p0 = cstart - 32;
-                for (int j = 32 - (K - 1); j < 32; ++j) {
-                    if (p0 + j >= s) {
-                        uint64_t c = (cww >> (2 * j)) & 3ull;
-                        cur = ((ivv >> j) & 1u) ? FR_EMPTY_KEY : (((cur << 2) & kmask) | c);
+                const uint32_t c0 = sh.codes[wi], c1 = sh.codes[wi + 1], c2 = sh.codes[wi + 2], c3 = sh.codes[wi + 3];
+                const uint64_t iv64 = ((uint64_t)sh.inv[wi] << 48) | ((uint64_t)sh.inv[wi + 1] << 32) |
+                                      ((uint64_t)sh.inv[wi + 2] << 16) | (uint64_t)sh.inv[wi + 3];
+                const uint32_t pm = (0xFFFFFFFFu >> (int)jl) & (jh == 32 ? 0xFFFFFFFFu : ~(0xFFFFFFFFu >> (int)jh));
+                uint32_t am = 0;                       // bit 31-j: the window ending at j holds a non-ACGT base
+                if (iv64) {
+                    for (int d = 0; d < K; ++d) am |= (uint32_t)(iv64 >> d);
+                }
+                if (!(dbg & 2)) pass = fr_filter32<WIDE>(c0, c1, c2, c3, kmask_lo, kmask_hi, tb.bloom, wsh, bsh);
+                pass = (pass & pm & ~am) | (pm & am & ~(uint32_t)iv64);
+                if (dbg & 1) pass = 0;
+            }
+            // ---- K3b: the warp queues its survivors' tile positions and drains them ----
+            {
+                uint16_t *wq = sh.queue + (tid >> 5) * (32 * FR_PPT);
+                int total;
+                int my = fr_warp_excl_scan(__popc(pass), lane, total);
+                if (total) {
+                    while (pass) {
+                        const int j = __clz(pass);
+                        wq[my++] = (uint16_t)(FR_PPT * tid + j);
+                        pass &= ~(0x80000000u >> j);
                     }
+                    __syncwarp();
+                    fr_warp_drain(sh, hl, tb, wq, total, lane, kmask);
                 }
             }
-#pragma unroll 1
-            for (int round = 0; round < FR_ROUNDS; ++round) {
-                if (warp_active) {
-#pragma unroll
-                    for (int jj = 0; jj < FR_PPR; ++jj) {
-                        const int j = round * FR_PPR + jj;
-                        const int64_t p = cstart + j;
-                        bool pass = false;
-                        if (active && p >= s) {
-                            uint64_t c = (cw >> (2 * j)) & 3ull;
-                            cur = ((ivw >> j) & 1u) ? FR_EMPTY_KEY : (((cur << 2) & kmask) | c);
-                            if (p >= lo && p < e && cur != FR_EMPTY_KEY) {
-                                uint64_t h = fr_hash(cur);
-                                uint32_t word = __ldg(&tb.bloom[fr_bloom_word(h, tb.lg_words)]);
-                                uint32_t m = fr_bloom_mask(h);
-                                pass = (word & m) == m;
-                            }
-                        }
-                        unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
-                        if (bal) {
-                            int base = 0;
-                            const int leader = __ffs(bal) - 1;
-                            if (lane == leader) base = atomicAdd(&sh.qcount, __popc(bal));
-                            base = __shfl_sync(0xFFFFFFFFu, base, leader);
-                            if (pass) sh.queue[base + __popc(bal & ((1u << lane) - 1))] = cur;
-                        }
+            __syncthreads();
+            if (sh.flag) {
+                // the hit list filled up: drop this tile's hits, make room, run the tile again
+                __syncthreads();
+                if (!compacted) {
+                    const int u = fr_block_sort_unique(hl.ptr, hc0, sh.scan);
+                    if (tid == 0) { sh.hcount = u; sh.flag = 0; }
+                    compacted = true;
+                } else {
+                    // migrate to a global slab that can hold one entry per lookup position
+                    long long need = 1;
+                    while (need < n_lookups) need <<= 1;
+                    if (tid == 0) sh.misc = (long long)atomicAdd(&counters[1], (unsigned long long)need);
+                    __syncthreads();
+                    const long long off = sh.misc;
+                    if (off + need > spill_cap) {
+                        if (tid == 0) atomicOr(&counters[2], FR_FLAG_SPILL_OVERFLOW);
+                        hl.dead = true;
+                    } else {
+                        uint32_t *dst = spill + off;
+                        for (int i = tid; i < hc0; i += FR_THREADS) dst[i] = hl.ptr[i];
+                        hl.ptr = dst;
+                        hl.cap = (int)(need > 0x40000000ll ? 0x40000000ll : need);
                     }
+                    if (tid == 0) { sh.hcount = hc0; sh.flag = 0; }
                 }
-                // barrier + uniform decision in one: the last thread to arrive sees the final count
-                if (__syncthreads_or(sh.qcount > FR_QCAP - FR_THREADS * FR_PPR))
-                    fr_flush(sh, hl, tb, n_lookups, spill, spill_cap, counters);
+                __syncthreads();
+                --tile;
+                continue;
             }
+            compacted = false;
         }
-        // ---- K3b/K3c: final drain, sort + unique, emit ----
-        fr_flush(sh, hl, tb, n_lookups, spill, spill_cap, counters);
-        int u = fr_block_sort_unique(hl.ptr, sh.hcount, sh.scan);
+        // ---- K3c: sort + unique, emit ----
+        __syncthreads();
+        int u = -1;
+        const int hc = sh.hcount;
+        if (dbg & 4) u = 0;
+        else if (hl.ptr == sh.hits && hc > 1 && tb.n > 0) u = fr_bucket_sort_unique(sh, hc, (uint32_t)tb.n);
+        if (u < 0) u = fr_block_sort_unique(hl.ptr, hc, sh.scan);
         if (hl.dead) u = 0;
         if (tid == 0) sh.misc = (long long)atomicAdd(&counters[0], (unsigned long long)u);
         __syncthreads();
@@ -352,14 +568,22 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
     if (grid < 1) grid = 1;
     static bool attr_set = false;
     if (!attr_set) {
-        FR_CUDA(ctx, cudaFuncSetAttribute(fr_extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        FR_CUDA(ctx, cudaFuncSetAttribute(fr_extract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(FrExtractShared)));
+        FR_CUDA(ctx, cudaFuncSetAttribute(fr_extract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(FrExtractShared)));
         attr_set = true;
     }
+    static const int dbg = getenv("FR_EXTRACT_DEBUG") ? atoi(getenv("FR_EXTRACT_DEBUG")) : 0;   // timing experiments only
     fr_kt_begin(ctx, "fr_extract_kernel", st);
-    fr_extract_kernel<<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
-        d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
-        ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters);
+    if (ctx->table.k <= 16)     // a k-mer fits one 32-bit word
+        fr_extract_kernel<false><<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
+            d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
+            ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
+    else
+        fr_extract_kernel<true><<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
+            d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
+            ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
     FR_LAUNCH_CHECK(ctx, "fr_extract_kernel");
     return FR_OK;
 }

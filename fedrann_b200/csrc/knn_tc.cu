@@ -594,12 +594,20 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
             uint32_t id[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) id[u] = 0xFFFFFFFFu - (uint32_t)cand[min(c0 + u, m - 1)];
+            // all 64 row elements of the 4 candidates are requested before the first FMA (the gather is
+            // L2-latency bound: what matters is the number of loads in flight per warp)
+            float v[4][16];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float *rp = En + (int64_t)id[u] * D + lane;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[u][i] = (lane + 32 * i < D) ? __ldg(rp + 32 * i) : 0.0f;
+            }
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                const int j = lane + 32 * i;
-                if (j < D) {
+                if (lane + 32 * i < D) {
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) acc[u] = fmaf(q[i], __ldg(En + (int64_t)id[u] * D + j), acc[u]);
+                    for (int u = 0; u < 4; ++u) acc[u] = fmaf(q[i], v[u][i], acc[u]);
                 }
             }
 #pragma unroll

@@ -5,21 +5,20 @@
 // never on the hash function or insertion order.
 #include "common.cuh"
 
-__global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64_t n,
-                                       uint64_t *keys, uint32_t *vals, uint32_t *bloom,
-                                       int lg_cap, int lg_words) {
+__global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64_t n, uint4 *slots,
+                                       uint32_t *bloom, int lg_cap, int lg_words) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    uint64_t key = codes[i];
-    uint64_t h = fr_hash(key);
-    atomicOr(&bloom[fr_bloom_word(h, lg_words)], fr_bloom_mask(h));
-    uint32_t cap_mask = (uint32_t)((1ull << lg_cap) - 1);
-    uint32_t slot = fr_table_slot(h, lg_cap);
+    const uint64_t key = codes[i];
+    const uint32_t bh = fr_bloom_hash((uint32_t)key, (uint32_t)(key >> 32));
+    atomicOr(&bloom[fr_bloom_word(bh, lg_words)], 0x80000000u >> fr_bloom_shift(bh, lg_words));
+    const uint32_t cap_mask = (uint32_t)((1ull << lg_cap) - 1);
+    uint32_t slot = fr_table_slot(fr_hash(key), lg_cap);
     while (true) {
-        unsigned long long old = atomicCAS((unsigned long long *)&keys[slot],
-                                           (unsigned long long)FR_EMPTY_KEY, (unsigned long long)key);
+        unsigned long long *kp = reinterpret_cast<unsigned long long *>(&slots[slot]);
+        unsigned long long old = atomicCAS(kp, (unsigned long long)FR_EMPTY_KEY, (unsigned long long)key);
         if (old == FR_EMPTY_KEY || old == key) {
-            atomicMin(&vals[slot], (uint32_t)i);  // duplicates keep the first occurrence
+            atomicMin(&slots[slot].z, (uint32_t)i);  // duplicates keep the first occurrence
             return;
         }
         slot = (slot + 1) & cap_mask;
@@ -39,32 +38,29 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     cudaStream_t st = (cudaStream_t)stream;
     FR_CUDA(ctx, cudaSetDevice(ctx->device));
     if (ctx->d_bloom) { cudaFree(ctx->d_bloom); ctx->d_bloom = nullptr; }
-    if (ctx->d_keys) { cudaFree(ctx->d_keys); ctx->d_keys = nullptr; }
-    if (ctx->d_vals) { cudaFree(ctx->d_vals); ctx->d_vals = nullptr; }
+    if (ctx->d_slots) { cudaFree(ctx->d_slots); ctx->d_slots = nullptr; }
     ctx->has_table = false;
-    int lg_cap = ceil_log2(n > 0 ? 2 * n : 1);
+    int lg_cap = ceil_log2(n > 0 ? (n * 10 + 6) / 7 : 1);   // load <= 0.7
     if (lg_cap < 10) lg_cap = 10;
-    int lg_words = lg_cap - 2;  // cap/4 words = 16..32 filter bits per key
+    int lg_words = ceil_log2(n > 0 ? n : 1);                // 32..64 filter bits per key
     if (lg_words < 8) lg_words = 8;
+    if (lg_words > 27) lg_words = 27;
     size_t cap = (size_t)1 << lg_cap, words = (size_t)1 << lg_words;
-    if (cudaMalloc(&ctx->d_keys, cap * 8) != cudaSuccess ||
-        cudaMalloc(&ctx->d_vals, cap * 4) != cudaSuccess ||
+    if (cudaMalloc(&ctx->d_slots, cap * 16) != cudaSuccess ||
         cudaMalloc(&ctx->d_bloom, words * 4) != cudaSuccess)
         return fr_fail(ctx, FR_ERR_NOMEM, "fr_table_build: cudaMalloc failed");
-    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_keys, 0xFF, cap * 8, st));
-    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_vals, 0xFF, cap * 4, st));
+    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_slots, 0xFF, cap * 16, st));
     FR_CUDA(ctx, cudaMemsetAsync(ctx->d_bloom, 0, words * 4, st));
     if (n > 0) {
         int threads = 256;
         int64_t blocks = (n + threads - 1) / threads;
         fr_kt_begin(ctx, "fr_table_insert_kernel", st);
-        fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_keys, ctx->d_vals,
-                                                                      ctx->d_bloom, lg_cap, lg_words);
+        fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_slots, ctx->d_bloom,
+                                                                      lg_cap, lg_words);
         FR_LAUNCH_CHECK(ctx, "fr_table_insert_kernel");
     }
     ctx->table.bloom = ctx->d_bloom;
-    ctx->table.keys = ctx->d_keys;
-    ctx->table.vals = ctx->d_vals;
+    ctx->table.slots = ctx->d_slots;
     ctx->table.lg_cap = lg_cap;
     ctx->table.lg_words = lg_words;
     ctx->table.k = k;

@@ -112,6 +112,36 @@ int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norm
 /* statistics of the last fr_knn call: rows that needed the exact fallback */
 int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
 
+/* ---- N1: canonical k-mer counting + seeded sampling ----
+ * Replaces the pre-step of run_kmer_searcher (fedrann/count_kmers.py:76-123:
+ * `jellyfish count -C`, `jellyfish dump -L <min-mult>`, the awk sampler).
+ * A canonical k-mer c (min of the k-mer and its reverse complement, codes A0 C1
+ * G2 T3) is sampled iff splitmix64(c ^ seed) < threshold (threshold =
+ * fraction * 2^64); windows with a non-ACGT base or crossing a read boundary
+ * are skipped.  begin() sizes and clears the count table (capacity = slots, a
+ * power of two is chosen >= capacity), add() may be called once per batch of
+ * reads and returns the number of distinct sampled k-mers so far (FR_ERR_NOMEM
+ * when the table is full: begin again with a larger capacity), export() writes
+ * the (code, count) pairs with count >= min_multiplicity in unspecified order;
+ * *n_out may exceed cap (nothing is written beyond cap). */
+int fr_kmer_count_begin(fr_ctx *ctx, int k, int64_t capacity, void *stream);
+int fr_kmer_count_add(fr_ctx *ctx, const uint8_t *d_bases, const int64_t *d_offsets, int64_t n_reads,
+                      uint64_t threshold, uint64_t seed, int64_t *distinct_out, void *stream);
+int fr_kmer_count_export(fr_ctx *ctx, int min_multiplicity, uint64_t *d_codes_out, uint32_t *d_counts_out,
+                         int64_t cap, int64_t *n_out, void *stream);
+
+/* ---- N2: overlaps.tsv (fedrann/__main__.py:261-300 + DataFrame.to_csv :385) ----
+ * One line per (row, neighbour != row) in row order then rank order:
+ * query_name, query_orientation (+/- for even/odd row), target_name,
+ * target_orientation, neighbor_rank (position in the unfiltered list), distance
+ * (shortest decimal that round-trips the float32, as numpy/pandas print it).
+ * names: read names of rows 0,2,4,... concatenated, name_offsets i64[n_rows/2+1].
+ * Negative neighbour ids wrap like Python's read_names[-1].  append != 0 skips the
+ * header and appends (rank-ordered multi-GPU output). */
+int fr_write_overlaps_tsv(const char *path, int append, const char *names, const int64_t *name_offsets,
+                          int64_t n_rows_total, int64_t row0, int64_t n_rows, int k, const int32_t *idx,
+                          const float *dist, int64_t *lines_out);
+
 #ifdef __cplusplus
 }
 #endif
