@@ -21,6 +21,7 @@ SYMBOLS = [
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
     "fr_table_build", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_last_fallback_rows",
+    "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
 ]
 
 
@@ -73,6 +74,11 @@ def lib():
     L.fr_knn.argtypes = [vp, vp, vp, vp, i64, i32, i32, i64, i64, i32, i32, vp, vp, vp]
     L.fr_knn_last_fallback_rows.argtypes = [vp]
     L.fr_knn_last_fallback_rows.restype = i64
+    u64 = C.c_uint64
+    L.fr_kmer_count_begin.argtypes = [vp, i32, i64, vp]
+    L.fr_kmer_count_add.argtypes = [vp, vp, vp, i64, u64, u64, C.POINTER(i64), vp]
+    L.fr_kmer_count_export.argtypes = [vp, i32, vp, vp, i64, C.POINTER(i64), vp]
+    L.fr_write_overlaps_tsv.argtypes = [C.c_char_p, i32, vp, vp, i64, i64, i64, i32, vp, vp, C.POINTER(i64)]
     _lib = L
     return L
 

@@ -79,7 +79,7 @@ __global__ void fr_kmer_export_kernel(const uint4 *__restrict__ slots, int64_t c
         uint4 v = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0, 0);
         if (i < cap) v = slots[i];
         const uint64_t key = ((uint64_t)v.y << 32) | v.x;
-        const bool keep = key != FR_EMPTY_KEY && (v.z + 1u) - 1u >= min_mult && v.z != 0xFFFFFFFFu;
+        const bool keep = key != FR_EMPTY_KEY && v.z >= min_mult;
         const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
         if (!bal) continue;
         unsigned long long base = 0;

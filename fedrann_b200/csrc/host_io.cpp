@@ -159,3 +159,82 @@ extern "C" int fr_write_frequency_bin(const char *path, const uint32_t *docfreq,
     fclose(f);
     return FR_OK;
 }
+
+// ---- N2: overlaps.tsv ----
+// get_output_dataframe (fedrann/__main__.py:261-300) + DataFrame.to_csv(sep="\t", index=False)
+// (:385) restated as one streaming writer.  A float32 distance is printed the way numpy/pandas
+// print it: the shortest decimal that round-trips, positional for 1e-4 <= |x| < 1e16 (with at
+// least one digit after the point), scientific (d.ddde-XX) otherwise.
+#include <charconv>
+
+namespace {
+inline int fmt_f32(float x, char *out) {
+    if (x != x) { memcpy(out, "nan", 3); return 3; }     // pandas' na_rep is "" -- never produced by the path
+    const float ax = x < 0 ? -x : x;
+    char *p = out;
+    if (ax != 0.0f && ((double)ax < 1e-4 || (double)ax >= 1e16)) {
+        auto r = std::to_chars(p, p + 48, x, std::chars_format::scientific);
+        return (int)(r.ptr - out);
+    }
+    auto r = std::to_chars(p, p + 48, x, std::chars_format::fixed);
+    bool dot = false;
+    for (char *q = p; q < r.ptr; ++q) dot |= (*q == '.');
+    if (!dot) { *r.ptr++ = '.'; *r.ptr++ = '0'; }
+    return (int)(r.ptr - out);
+}
+// csv.QUOTE_MINIMAL as pandas applies it: a field holding the delimiter, a quote or a line break
+// is wrapped in double quotes, embedded quotes doubled
+inline void put_field(std::vector<char> &buf, const char *s, size_t n) {
+    bool q = false;
+    for (size_t i = 0; i < n; ++i) q |= (s[i] == '\t' || s[i] == '"' || s[i] == '\n' || s[i] == '\r');
+    if (!q) { buf.insert(buf.end(), s, s + n); return; }
+    buf.push_back('"');
+    for (size_t i = 0; i < n; ++i) { if (s[i] == '"') buf.push_back('"'); buf.push_back(s[i]); }
+    buf.push_back('"');
+}
+}  // namespace
+
+extern "C" int fr_write_overlaps_tsv(const char *path, int append, const char *names, const int64_t *name_offsets,
+                                     int64_t n_rows_total, int64_t row0, int64_t n_rows, int k, const int32_t *idx,
+                                     const float *dist, int64_t *lines_out) {
+    if (!path || !names || !name_offsets || n_rows < 0 || k < 0 || (n_rows > 0 && (!idx || !dist))) return FR_ERR_ARG;
+    FILE *f = fopen(path, append ? "ab" : "wb");
+    if (!f) return FR_ERR_ARG;
+    std::vector<char> buf;
+    buf.reserve((1u << 22) + 4096);
+    if (!append) {
+        static const char hdr[] = "query_name\tquery_orientation\ttarget_name\ttarget_orientation\tneighbor_rank\tdistance\n";
+        buf.insert(buf.end(), hdr, hdr + sizeof(hdr) - 1);
+    }
+    int64_t lines = 0;
+    char num[64];
+    for (int64_t i = 0; i < n_rows; ++i) {
+        const int64_t q = row0 + i;
+        const char *qn = names + name_offsets[q >> 1];
+        const size_t ql = (size_t)(name_offsets[(q >> 1) + 1] - name_offsets[q >> 1]);
+        for (int j = 0; j < k; ++j) {
+            int64_t t = idx[i * k + j];
+            if (t == q) continue;                                 // :279-280
+            if (t < 0) t += n_rows_total;                         // Python's read_names[-1]
+            if (t < 0 || t >= n_rows_total) { fclose(f); return FR_ERR_ARG; }
+            const char *tn = names + name_offsets[t >> 1];
+            const size_t tl = (size_t)(name_offsets[(t >> 1) + 1] - name_offsets[t >> 1]);
+            put_field(buf, qn, ql);
+            buf.push_back('\t'); buf.push_back((q & 1) ? '-' : '+'); buf.push_back('\t');
+            put_field(buf, tn, tl);
+            buf.push_back('\t'); buf.push_back((t & 1) ? '-' : '+'); buf.push_back('\t');
+            auto r = std::to_chars(num, num + 16, j);
+            buf.insert(buf.end(), num, r.ptr);
+            buf.push_back('\t');
+            const int n = fmt_f32(dist[i * k + j], num);
+            buf.insert(buf.end(), num, num + n);
+            buf.push_back('\n');
+            ++lines;
+        }
+        if (buf.size() >= (1u << 22)) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
+    }
+    if (!buf.empty()) fwrite(buf.data(), 1, buf.size(), f);
+    fclose(f);
+    if (lines_out) *lines_out = lines;
+    return FR_OK;
+}

@@ -78,6 +78,28 @@ def write_frequency_bin(path: str, docfreq: np.ndarray) -> None:
           "fr_write_frequency_bin")
 
 
+def write_overlaps_tsv(path: str, names, idx: np.ndarray, dist: np.ndarray, *, row0: int = 0,
+                       n_rows_total: int | None = None, append: bool = False) -> int:
+    """overlaps.tsv exactly as get_output_dataframe + to_csv write it (__main__.py:261-300, :385).
+    names: one name per READ (rows 2r / 2r+1 are its + / - orientation).  Returns the line count."""
+    L = _lib.lib()
+    enc = [n.encode() for n in names]
+    noff = np.zeros(len(enc) + 1, dtype=np.int64)
+    np.cumsum([len(e) for e in enc], out=noff[1:])
+    blob = b"".join(enc) or b"\0"
+    idx = np.ascontiguousarray(idx, dtype=np.int32)
+    dist = np.ascontiguousarray(dist, dtype=np.float32)
+    n_rows, k = idx.shape if idx.ndim == 2 else (0, 0)
+    total = 2 * len(enc) if n_rows_total is None else n_rows_total
+    lines = C.c_int64(0)
+    rc = L.fr_write_overlaps_tsv(path.encode(), 1 if append else 0, C.c_char_p(blob),
+                                 noff.ctypes.data_as(C.c_void_p), total, row0, n_rows, k,
+                                 idx.ctypes.data_as(C.c_void_p), dist.ctypes.data_as(C.c_void_p), C.byref(lines))
+    if rc != 0:
+        raise FedrannError(f"fr_write_overlaps_tsv: {rc}")
+    return lines.value
+
+
 # ---------------------------------------------------------------------------
 class Engine:
     def __init__(self, device: int | None = None):
@@ -129,6 +151,35 @@ class Engine:
         if dtype is not None:
             t = t.to(dtype)
         return t.to(f"cuda:{self.device}", non_blocking=True)
+
+    # -- N1 --------------------------------------------------------------
+    def count_kmers(self, bases: torch.Tensor, offsets: torch.Tensor, k: int, fraction: float, seed: int,
+                    min_multiplicity: int = 1, capacity: int | None = None):
+        """Canonical k-mer counts of the sampled k-mers (replaces jellyfish count/dump + the awk
+        sampler, count_kmers.py:76-123).  -> (codes uint64 numpy, counts uint32 numpy), unordered."""
+        thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
+        n_pos = int(bases.numel())
+        if capacity is None:
+            capacity = int(min(4 ** min(k, 31), 2.5 * fraction * n_pos + 65536)) + 1024
+        R = offsets.numel() - 1
+        while True:
+            check(self.h, self.L.fr_kmer_count_begin(self.h, k, capacity, _stream()), "fr_kmer_count_begin")
+            distinct = C.c_int64(0)
+            rc = self.L.fr_kmer_count_add(self.h, _ptr(bases), _ptr(offsets), R, thr, seed & (2 ** 64 - 1),
+                                          C.byref(distinct), _stream())
+            if rc == -4 and capacity < (1 << 33):      # table full: grow and recount
+                capacity *= 4
+                continue
+            check(self.h, rc, "fr_kmer_count_add")
+            break
+        n = C.c_int64(0)
+        cap = max(distinct.value, 1)
+        codes = torch.empty(cap, dtype=torch.int64, device=bases.device)
+        counts = torch.empty(cap, dtype=torch.int32, device=bases.device)
+        check(self.h, self.L.fr_kmer_count_export(self.h, min_multiplicity, _ptr(codes), _ptr(counts), cap,
+                                                  C.byref(n), _stream()), "fr_kmer_count_export")
+        m = min(n.value, cap)
+        return codes[:m].cpu().numpy().view(np.uint64), counts[:m].cpu().numpy().view(np.uint32)
 
     # -- K2 --------------------------------------------------------------
     def build_table(self, codes, k: int) -> None:

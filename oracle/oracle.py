@@ -303,3 +303,71 @@ def knn_blas(Xn: np.ndarray, norms: np.ndarray, q0: int, q1: int, k: int, block:
         idx[a - q0:b - q0, :kk] = np.take_along_axis(part, order, axis=1)
         dist[a - q0:b - q0, :kk] = np.take_along_axis(pd, order, axis=1)
     return idx, dist
+
+
+# ---------------------------------------------------------------------------
+# N1 / N2: the callers either side of the path
+# ---------------------------------------------------------------------------
+def _splitmix64(x):
+    x = x.astype(np.uint64, copy=True)
+    with np.errstate(over="ignore"):
+        x += np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    return x
+
+
+def count_kmers(bases: np.ndarray, offsets: np.ndarray, k: int, fraction: float, min_mult: int, seed: int):
+    """What `jellyfish count -C` + `jellyfish dump -L min_mult` + a sampler produce
+    (fedrann/count_kmers.py:76-123): canonical k-mers (min of k-mer and reverse complement,
+    A0 C1 G2 T3) of every read, windows with a non-ACGT base skipped, multiplicity >= min_mult.
+    The reference's awk rand() sampler is unpinned; the build's sampler is
+    keep(c) <=> splitmix64(c ^ seed) < fraction * 2^64.  -> {code: count} (plain Python loop:
+    small inputs only)."""
+    code = {65: 0, 67: 1, 71: 2, 84: 3, 97: 0, 99: 1, 103: 2, 116: 3}
+    mask = (1 << (2 * k)) - 1
+    counts = {}
+    for r in range(len(offsets) - 1):
+        fw = rc = 0
+        run = 0
+        for b in bases[offsets[r]:offsets[r + 1]].tolist():
+            c = code.get(b)
+            if c is None:
+                run = 0
+                continue
+            fw = ((fw << 2) | c) & mask
+            rc = (rc >> 2) | ((3 - c) << (2 * (k - 1)))
+            run += 1
+            if run >= k:
+                can = min(fw, rc)
+                counts[can] = counts.get(can, 0) + 1
+    keys = np.array(sorted(counts), dtype=np.uint64)
+    thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
+    h = _splitmix64(keys ^ np.uint64(seed & (2 ** 64 - 1)))
+    return {int(c): counts[int(c)] for c, hh in zip(keys, h) if int(hh) < thr and counts[int(c)] >= min_mult}
+
+
+def overlaps_tsv(neighbor_matrix: np.ndarray, neighbor_distances: np.ndarray, read_names, strands) -> str:
+    """get_output_dataframe (fedrann/__main__.py:261-300) followed by
+    df.to_csv(path, sep="\\t", index=False) (:385), returned as text."""
+    import io
+    import pandas as pd
+    query_names, target_names, ranks, distances, qo, to = [], [], [], [], [], []
+    for query_index in range(neighbor_matrix.shape[0]):
+        for rank, target_index in enumerate(neighbor_matrix[query_index]):
+            if target_index == query_index:
+                continue
+            query_names.append(read_names[query_index])
+            qo.append(["+", "-"][strands[query_index]])
+            target_names.append(read_names[target_index])
+            to.append(["+", "-"][strands[target_index]])
+            ranks.append(rank)
+            distances.append(neighbor_distances[query_index][rank])
+    df = pd.DataFrame({"query_name": query_names, "query_orientation": qo, "target_name": target_names,
+                       "target_orientation": to, "neighbor_rank": ranks, "distance": distances})
+    if len(df) == 0:
+        df = df.astype({"neighbor_rank": "int64", "distance": "float32"})
+    buf = io.StringIO()
+    df.to_csv(buf, sep="\t", index=False)
+    return buf.getvalue()
