@@ -231,8 +231,22 @@ class CpuPipeline:
 
 
 # ---------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the real stdout; everything else a native library prints there
+    (NCCL's version banner) was redirected to stderr at start-up."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     from fedrann_b200.parallel import init_from_env
@@ -258,7 +272,8 @@ def main():
     # untimed set-up, then times host code only)
     wl = Workload(args.workload, rank_eff, world_eff, dev)
     eng = Engine(local)
-    eng.build_table(wl.lib.all_codes(), w["k"])
+    # the library is a hash-threshold sample (what N1 produces): declared to the engine, which verifies it
+    eng.build_table(wl.lib.all_codes(), w["k"], sampler=(w["seed"], w["fraction"]))
     P_dev = eng.upload_projection(wl.P)
     offsets_d = torch.from_numpy(wl.offsets).to(dev)
     nk, k_nn = wl.lib.nk, w["knn_k"]
@@ -270,7 +285,8 @@ def main():
               "parallelism": "reads sharded over %d GPU(s), one all-gather of embeddings" % world_eff,
               "l2": "inputs (%.0f MB of reads per rank) streamed once per step; 256 MiB L2 flush between steps"
                     % (wl.bases.numel() / 1e6),
-              "knn_mode": "tcgen05+rerank" if args.knn_mode == 0 else "fp32 scan"}
+              "knn_mode": "tcgen05+rerank" if args.knn_mode == 0 else "fp32 scan",
+              "library": "hash-threshold sample, verified on device" if eng.sampled else "arbitrary"}
 
     def device_step(timers=None):
         return run_hot_path(eng, wl.bases, offsets_d, P_dev, nk, k_nn, mode=args.knn_mode, group=group,
@@ -287,7 +303,7 @@ def main():
                 "impl": "reference", "config": config, "cpu_baseline": out["cpu_baseline"],
                 "e2e": {"value": out["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return 0
 
     # ------------------------------------------------------------------ native arm
@@ -373,7 +389,7 @@ def main():
                 "stage_ms": stage_ms,
                 "kernels_ms_per_step": {k: v[1] / args.steps for k, v in ktimes.items()},
                 "knn_fallback_rows": eng.knn_fallback_rows}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -19,7 +19,7 @@ SYMBOLS = [
     "fr_version", "fr_create", "fr_destroy", "fr_last_error", "fr_launch_count",
     "fr_profile_enable", "fr_profile_read",
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
-    "fr_table_build", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
+    "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_last_fallback_rows",
     "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
 ]
@@ -75,6 +75,7 @@ def lib():
     L.fr_knn_last_fallback_rows.argtypes = [vp]
     L.fr_knn_last_fallback_rows.restype = i64
     u64 = C.c_uint64
+    L.fr_table_set_sampler.argtypes = [vp, u64, u64, vp]
     L.fr_kmer_count_begin.argtypes = [vp, i32, i64, vp]
     L.fr_kmer_count_add.argtypes = [vp, vp, vp, i64, u64, u64, C.POINTER(i64), vp]
     L.fr_kmer_count_export.argtypes = [vp, i32, vp, vp, i64, C.POINTER(i64), vp]

@@ -127,7 +127,7 @@ def run_kmer_searcher(input_path: str, k: int, sample_fraction: float, min_multi
     _, first = np.unique(all_codes, return_index=True)
     if len(first) != len(all_codes):
         all_codes = all_codes[np.sort(first)]
-    eng.build_table(all_codes, k)
+    eng.build_table(all_codes, k, sampler=(global_variables.seed, sample_fraction))
     docfreq = torch.zeros(max(len(all_codes), 1), dtype=torch.int32, device=dev)
     indptr, indices = eng.extract(bases_d, offsets_d, docfreq)
 

@@ -23,6 +23,12 @@ struct FrTable {
     int lg_cap;    // log2(#table slots)
     int k;
     int64_t n;     // number of features F
+    // Set by fr_table_set_sampler once VERIFIED on the device: every key's canonical form c
+    // satisfies splitmix64(c ^ seed) < threshold (the library is a hash-threshold sample, as N1
+    // produces it).  K3 then rejects a position whose canonical k-mer fails that test in
+    // registers, without touching the filter.
+    int sampled;
+    uint64_t seed, threshold;
 };
 
 struct fr_ctx {
@@ -100,6 +106,12 @@ __device__ __forceinline__ uint64_t fr_hash(uint64_t kmer) {
 }
 __device__ __forceinline__ uint32_t fr_table_slot(uint64_t h, int lg_cap) {
     return (uint32_t)(h >> (64 - lg_cap));
+}
+__device__ __forceinline__ uint64_t fr_splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
 }
 // Filter hash: 32-bit multiplicative.  k-mers of k <= 16 fit one word (hi == 0).
 #define FR_BLOOM_MUL1 0x9E3779B1u

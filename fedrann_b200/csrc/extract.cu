@@ -121,6 +121,7 @@ struct FrExtractShared {
     uint32_t tmp[FR_HCAP];      // K3c: hits grouped by bucket
     uint32_t codes[FR_NWORDS];
     uint32_t inv[FR_NWORDS];
+    uint32_t rcodes[FR_NWORDS]; // complemented codes, first base least significant (sampled libraries only)
     uint16_t queue[FR_QCAP];
     int bcnt[FR_MAXB + 1];      // K3c: bucket sizes -> unique counts
     int bstart[FR_MAXB + 1];
@@ -368,7 +369,51 @@ __device__ __forceinline__ uint32_t fr_filter32(uint32_t c0, uint32_t c1, uint32
     return pass;
 }
 
+// The same for a library that is a verified hash-threshold sample (FrTable::sampled): a position
+// can only hit when its CANONICAL k-mer passes the sampler's test, which needs no memory access.
+// The reverse complement comes from a second packed stream (complemented codes, first base in
+// the LEAST significant bits): q0..q3 = that stream for the thread's 64 positions, already
+// shifted right by 2*(33-K) bits, so that the reverse complement of the k-mer ending at
+// position j is (q3:q2:q1:q0) >> 2j.
 template <bool WIDE>
+__device__ __forceinline__ uint32_t fr_filter32_sampled(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                        uint32_t q0, uint32_t q1, uint32_t q2, uint32_t q3,
+                                                        uint32_t kmask_lo, uint32_t kmask_hi, uint64_t seed,
+                                                        uint64_t threshold) {
+    uint32_t pass = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const int s = 62 - 2 * j;
+        uint32_t lo, hi = 0, rlo, rhi = 0;
+        if (s >= 32) {
+            lo = __funnelshift_r(c2, c1, s - 32);
+            if (WIDE) hi = __funnelshift_r(c1, c0, s - 32);
+        } else {
+            lo = __funnelshift_r(c3, c2, s);
+            if (WIDE) hi = __funnelshift_r(c2, c1, s);
+        }
+        if (2 * j >= 32) {
+            rlo = __funnelshift_r(q1, q2, 2 * j - 32);
+            if (WIDE) rhi = __funnelshift_r(q2, q3, 2 * j - 32);
+        } else {
+            rlo = __funnelshift_r(q0, q1, 2 * j);
+            if (WIDE) rhi = __funnelshift_r(q1, q2, 2 * j);
+        }
+        uint64_t fw, rc;
+        if (WIDE) {
+            fw = ((uint64_t)(hi & kmask_hi) << 32) | lo;
+            rc = ((uint64_t)(rhi & kmask_hi) << 32) | rlo;
+        } else {
+            fw = lo & kmask_lo;
+            rc = rlo & kmask_lo;
+        }
+        const uint64_t can = fw < rc ? fw : rc;
+        pass = (pass << 1) | (fr_splitmix64(can ^ seed) < threshold ? 1u : 0u);
+    }
+    return pass;
+}
+
+template <bool WIDE, bool SAMPLED>
 __global__ void __launch_bounds__(FR_THREADS, 4)
 fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int64_t *__restrict__ offsets,
                   int64_t n_reads, FrTable tb, int32_t *scratch, int64_t scratch_cap, uint32_t *spill,
@@ -421,6 +466,11 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 }
                 sh.codes[w] = c;
                 sh.inv[w] = iv;
+                if (SAMPLED) {      // reverse the 2-bit groups and complement
+                    uint32_t rv = __brev(c);
+                    rv = ((rv >> 1) & 0x55555555u) | ((rv & 0x55555555u) << 1);
+                    sh.rcodes[w] = ~rv;
+                }
             }
             __syncthreads();
             // ---- K3a: filter (warps run on their own from here to the end of the tile) ----
@@ -437,7 +487,19 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 if (iv64) {
                     for (int d = 0; d < K; ++d) am |= (uint32_t)(iv64 >> d);
                 }
-                if (!(dbg & 2)) pass = fr_filter32<WIDE>(c0, c1, c2, c3, kmask_lo, kmask_hi, tb.bloom, wsh, bsh);
+                if (SAMPLED) {
+                    // reverse-complement stream of the same 64 positions, shifted right by 2*(33-K) bits
+                    const uint32_t r0 = sh.rcodes[wi], r1 = sh.rcodes[wi + 1], r2 = sh.rcodes[wi + 2],
+                                   r3 = sh.rcodes[wi + 3];
+                    const int bs = 2 * (33 - K), wo = bs >> 5, bb = bs & 31;
+                    const uint32_t t0 = wo == 0 ? r0 : (wo == 1 ? r1 : r2), t1 = wo == 0 ? r1 : (wo == 1 ? r2 : r3),
+                                   t2 = wo == 0 ? r2 : (wo == 1 ? r3 : 0u), t3 = wo == 0 ? r3 : 0u;
+                    const uint32_t q0 = __funnelshift_r(t0, t1, bb), q1 = __funnelshift_r(t1, t2, bb),
+                                   q2 = __funnelshift_r(t2, t3, bb), q3 = t3 >> bb;
+                    pass = fr_filter32_sampled<WIDE>(c0, c1, c2, c3, q0, q1, q2, q3, kmask_lo, kmask_hi, tb.seed,
+                                                     tb.threshold);
+                } else if (!(dbg & 2))
+                    pass = fr_filter32<WIDE>(c0, c1, c2, c3, kmask_lo, kmask_hi, tb.bloom, wsh, bsh);
                 pass = (pass & pm & ~am) | (pm & am & ~(uint32_t)iv64);
                 if (dbg & 1) pass = 0;
             }
@@ -566,24 +628,24 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
     (void)d_docfreq;
     int64_t grid = n_reads < (int64_t)ctx->sm_count * 64 ? n_reads : (int64_t)ctx->sm_count * 64;
     if (grid < 1) grid = 1;
+    typedef void (*KernelFn)(const uint8_t *, int64_t, const int64_t *, int64_t, FrTable, int32_t *, int64_t, uint32_t *,
+                             int64_t, int64_t *, int32_t *, unsigned long long *, int);
+    static const KernelFn fns[4] = {fr_extract_kernel<false, false>, fr_extract_kernel<true, false>,
+                                    fr_extract_kernel<false, true>, fr_extract_kernel<true, true>};
     static bool attr_set = false;
     if (!attr_set) {
-        FR_CUDA(ctx, cudaFuncSetAttribute(fr_extract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(FrExtractShared)));
-        FR_CUDA(ctx, cudaFuncSetAttribute(fr_extract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(FrExtractShared)));
+        for (int i = 0; i < 4; ++i)
+            FR_CUDA(ctx, cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)sizeof(FrExtractShared)));
         attr_set = true;
     }
     static const int dbg = getenv("FR_EXTRACT_DEBUG") ? atoi(getenv("FR_EXTRACT_DEBUG")) : 0;   // timing experiments only
+    // a k-mer of k <= 16 fits one 32-bit word; a verified sampled library skips the filter loads
+    const KernelFn fn = fns[(ctx->table.k > 16 ? 1 : 0) + (ctx->table.sampled && !(dbg & 8) ? 2 : 0)];
     fr_kt_begin(ctx, "fr_extract_kernel", st);
-    if (ctx->table.k <= 16)     // a k-mer fits one 32-bit word
-        fr_extract_kernel<false><<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
-            d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
-            ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
-    else
-        fr_extract_kernel<true><<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
-            d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
-            ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
+    fn<<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
+        d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
+        ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
     FR_LAUNCH_CHECK(ctx, "fr_extract_kernel");
     return FR_OK;
 }

@@ -42,7 +42,7 @@ constexpr int TC_ABLK = TC_M * TC_KB * 2;        // 16 KB per resident A block
 constexpr int TC_NS = 256;                       // database rows per B stage / per MMA (N=128 MMAs are smem-bound)
 constexpr int TC_STAGE = TC_NS * TC_KB * 2;      // 32 KB per B stage
 constexpr int TC_STASH = 0;                      // (no shared-memory stash: hit columns are replayed from registers)
-constexpr int TC_ROWST = TC_M * 8;               // per-row threshold + append counter
+constexpr int TC_ROWST = TC_M * 4 * (1 + TC_EPQ); // per-row threshold + one append counter per quadrant warp
 constexpr int TC_MAX_STAGES = 8;
 constexpr int TC_MAX_KBLKS = 8;                  // Dp <= 512 keeps the query tile resident
 constexpr int TC_MAX_SLOTS = 6;
@@ -153,14 +153,18 @@ __device__ __forceinline__ unsigned long long tc_key(float score, uint32_t idx) 
 // exact keep_lo largest keys (ties broken by lower database index).  All 32 lanes call it
 // with the same arguments.
 template <int KPL>
-__device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n, int keep_lo, int keep_hi, int *kept) {
+__device__ __noinline__ float tc_warp_select(unsigned long long *buf, int n0, int n1, int keep_lo, int keep_hi,
+                                             int *kept) {
+    // the row's keys sit at buf[0..n0) (appended upwards by the quadrant's first warp) and at
+    // buf[32*KPL-1 .. 32*KPL-n1] (appended downwards by its second warp)
     const int lane = threadIdx.x & 31;
+    const int n = n0 + n1;
     uint32_t hi[KPL], lo[KPL];
     uint32_t mx = 0, mn = 0xFFFFFFFFu;
 #pragma unroll
     for (int i = 0; i < KPL; ++i) {
         const int j = lane + 32 * i;
-        unsigned long long key = j < n ? __ldcg(buf + j) : 0ull;
+        unsigned long long key = j < n ? __ldcg(buf + (j < n0 ? j : 32 * KPL - 1 - (j - n0))) : 0ull;
         hi[i] = (uint32_t)(key >> 32);
         lo[i] = (uint32_t)key;
         mx = max(mx, hi[i]);
@@ -238,42 +242,34 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 
 // Epilogue inner step: 16 scores of one query row (this thread's TMEM lane) against the row's
-// threshold.  The chunk maximum is tested first; only when some lane of the warp has a score
-// above its threshold does each lane build a 16-bit hit mask and walk its own set bits; the
-// warp's cost is the largest hit count among its lanes.  Append positions are reserved once
-// per chunk from a shared-memory counter (the warps of one TMEM lane quadrant share rows).
+// threshold.  The 16-bit hit mask is built without predicates: the sign bit of (thr - score)
+// is set exactly when score > thr, and a funnel shift moves it into the mask (2 instructions
+// per score).  Each lane then walks ITS OWN set bits (the warp's cost is the largest hit count
+// among its lanes) and appends at a position it keeps in a register: the two warps of a TMEM
+// lane quadrant fill the row's buffer from opposite ends, so no atomic is needed.
 __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *buf, int *cnt, float thr) {
-    float m = -INFINITY;
+                                            unsigned long long *ptr, int step, int &pos, float thr) {
+    uint32_t mask = 0;
 #pragma unroll
-    for (int g = 0; g < 4; ++g)
-        m = fmaxf(m, fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
-                           fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]))));
-    if (__any_sync(0xFFFFFFFFu, m > thr)) {
-        uint32_t mask = 0;
+    for (int j = 15; j >= 0; --j) mask = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[j])), mask, 1);
+    if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
+        const int64_t left = n_db - (int64_t)cbase;
+        mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
+    }
+    while (mask) {
+        // the value is picked from the registers by a 4-level select tree on the bits of j
+        // (no dynamic register indexing)
+        const int j = __ffs(mask) - 1;
+        mask &= mask - 1;
+        uint32_t a8[8], a4[4];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) mask |= (__uint_as_float(v[j]) > thr ? 1u : 0u) << j;
-        if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
-            const int64_t left = n_db - (int64_t)cbase;
-            mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
-        }
-        if (mask) {
-            // one reservation per chunk, then this lane walks ITS OWN hits; the value is picked from
-            // the registers by a 4-level select tree on the bits of j (no dynamic register indexing)
-            int pos = atomicAdd(cnt, __popc(mask));
-            do {
-                const int j = __ffs(mask) - 1;
-                mask &= mask - 1;
-                uint32_t a8[8], a4[4];
+        for (int i = 0; i < 8; ++i) a8[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) a8[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = (j & 2) ? a8[2 * i + 1] : a8[2 * i];
-                const uint32_t b0 = (j & 4) ? a4[1] : a4[0], b1 = (j & 4) ? a4[3] : a4[2];
-                const uint32_t x = (j & 8) ? b1 : b0;
-                buf[pos++] = tc_key(__uint_as_float(x), cbase + j);
-            } while (mask);
-        }
+        for (int i = 0; i < 4; ++i) a4[i] = (j & 2) ? a8[2 * i + 1] : a8[2 * i];
+        const uint32_t b0 = (j & 4) ? a4[1] : a4[0], b1 = (j & 4) ? a4[3] : a4[2];
+        const uint32_t x = (j & 8) ? b1 : b0;
+        ptr[step * pos] = tc_key(__uint_as_float(x), cbase + j);
+        ++pos;
     }
 }
 
@@ -316,7 +312,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
 
     const int cta = blockIdx.x;
     const bool dbg_on = p.dbg != nullptr;
-    long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0;
+    long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0, n_cmp = 0;
     const long long t_start = clock64();
     const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
     const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
@@ -392,8 +388,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         const int sub = (warp - 2) >> 2;                 // which of the quadrant's warps
         const int row_in_tile = quad * 32 + lane;
         float *s_thr = reinterpret_cast<float *>(gbase + (sRow - base));
-        int *s_cnt = reinterpret_cast<int *>(s_thr + TC_M);
+        int *s_cnt = reinterpret_cast<int *>(s_thr + TC_M);      // [TC_EPQ][TC_M]: entries appended by each warp
         const int bar_id = 1 + quad;
+        const int step = sub ? -1 : 1;
         uint32_t tile = 0;
         for (int64_t u = u_begin; u < u_end;) {
             const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
@@ -403,7 +400,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
             const int64_t stream = (valid ? grow : 0) * p.slots + slot;
             unsigned long long *buf = p.keys + stream * CAP;
-            if (sub == 0) { s_thr[row_in_tile] = valid ? -INFINITY : INFINITY; s_cnt[row_in_tile] = 0; }
+            unsigned long long *ptr = sub ? buf + CAP - 1 : buf;     // this warp's end of the row's buffer
+            int mycnt = 0;
+            if (sub == 0) s_thr[row_in_tile] = valid ? -INFINITY : INFINITY;
             tc_quad_bar(bar_id);
             for (int64_t t = t0; t < t1; ++t, ++tile) {
                 const uint32_t ab = tile & 1;
@@ -421,39 +420,55 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     tc_ld_wait();                                          // va landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
                     tc_ld16(taddr + (c + TC_EPQ) * TC_CH, vb);             // next own chunk in flight
-                    tc_filter16(va, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, buf, s_cnt + row_in_tile, thr);
+                    tc_filter16(va, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
                     if (c + 2 * TC_EPQ < TC_N / TC_CH) tc_ld16(taddr + (c + 2 * TC_EPQ) * TC_CH, va);
-                    tc_filter16(vb, (uint32_t)(col0 + (c + TC_EPQ) * TC_CH), ragged, p.n_db, buf,
-                                s_cnt + row_in_tile, thr);
+                    tc_filter16(vb, (uint32_t)(col0 + (c + TC_EPQ) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
                 tc_fence_before();
+                s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
-                tc_quad_bar(bar_id);                     // every append of this tile is visible
+                tc_quad_bar(bar_id);                     // every append of this tile and both counts are visible
                 if (dbg_on) { const long long t2 = clock64(); e_bar += t2 - tb; tb = t2; }
                 // a buffer that could overflow during the next tile is compacted now
-                unsigned need = __ballot_sync(0xFFFFFFFFu, s_cnt[row_in_tile] > CAP - TC_N);
-                while (need) {
-                    const int src = __ffs(need) - 1;
-                    need &= need - 1;
-                    if (src % TC_EPQ != sub) continue;   // the quadrant's other warp takes this row
-                    const int n = __shfl_sync(0xFFFFFFFFu, s_cnt[row_in_tile], src);
-                    const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
-                    int kept;
-                    const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n, p.klo,
-                                                              p.khi, &kept);
-                    if (lane == src) { s_thr[row_in_tile] = nt; s_cnt[row_in_tile] = kept; }
+                const int c0r = s_cnt[row_in_tile], c1r = s_cnt[TC_M + row_in_tile];
+                unsigned need = __ballot_sync(0xFFFFFFFFu, c0r + c1r > CAP - TC_N);
+                tc_quad_bar(bar_id);                     // both warps hold the same counts before either rewrites them
+                if (need) {
+                    unsigned mine = need;
+                    while (mine) {
+                        const int src = __ffs(mine) - 1;
+                        mine &= mine - 1;
+                        if (src % TC_EPQ != sub) continue;   // the quadrant's other warp takes this row
+                        const int n0 = __shfl_sync(0xFFFFFFFFu, c0r, src), n1 = __shfl_sync(0xFFFFFFFFu, c1r, src);
+                        const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
+                        int kept;
+                        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n0, n1,
+                                                                  p.klo, p.khi, &kept);
+                        if (lane == src) {
+                            s_thr[row_in_tile] = nt;
+                            s_cnt[row_in_tile] = kept;
+                            s_cnt[TC_M + row_in_tile] = 0;
+                        }
+                        if (dbg_on && lane == 0) ++n_cmp;
+                    }
+                    if (dbg_on) { const long long t2 = clock64(); e_cmp += t2 - tb; tb = t2; }
+                    tc_quad_bar(bar_id);                 // new thresholds / counts are visible
+                    mycnt = s_cnt[sub * TC_M + row_in_tile];
+                    if (dbg_on) e_bar += clock64() - tb;
                 }
-                if (dbg_on) { const long long t2 = clock64(); e_cmp += t2 - tb; tb = t2; }
-                tc_quad_bar(bar_id);                     // new thresholds / counts are visible
-                if (dbg_on) e_bar += clock64() - tb;
             }
-            if (sub == 0 && valid) { p.counts[stream] = s_cnt[row_in_tile]; p.thrs[stream] = s_thr[row_in_tile]; }
+            if (sub == 0 && valid) {
+                // [15:0] keys at the front of the buffer, [31:16] keys at its end
+                p.counts[stream] = s_cnt[row_in_tile] | (s_cnt[TC_M + row_in_tile] << 16);
+                p.thrs[stream] = s_thr[row_in_tile];
+            }
+            tc_quad_bar(bar_id);                         // the next segment resets the row state
             u += t1 - t0;
         }
     }
@@ -467,6 +482,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             atomicAdd(&p.dbg[3], (unsigned long long)w0); atomicAdd(&p.dbg[4], (unsigned long long)(life - w0));
             atomicAdd(&p.dbg[8], (unsigned long long)e_ld); atomicAdd(&p.dbg[9], (unsigned long long)e_flt);
             atomicAdd(&p.dbg[10], (unsigned long long)e_bar); atomicAdd(&p.dbg[11], (unsigned long long)e_cmp);
+            atomicAdd(&p.dbg[12], (unsigned long long)n_cmp);
         }
         if (warp == 0) atomicAdd(&p.dbg[5], (unsigned long long)life);
     }
@@ -531,12 +547,13 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
         float tau = -INFINITY;      // largest final threshold of a buffer that ever dropped something
         bool ok = true;
         for (int s = 0; s < slots; ++s) {
-            const int c = counts[row * slots + s];
+            const int cc = counts[row * slots + s];
+            const int c0 = cc & 0xFFFF, c = c0 + (cc >> 16);      // front part, total (rest sits at the end)
             if (c == 0) continue;
             tau = fmaxf(tau, thrs[row * slots + s]);
             if (n + c > max_n) { ok = false; break; }
             const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
-            for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + i);
+            for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0)));
             n += c;
         }
         __syncwarp();
@@ -758,8 +775,8 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
                 h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / (4e6 * TC_EPQ), h[4] / n / (4e6 * TC_EPQ),
                 (double)p.units / n);
         const double ew = n * 4e6 * TC_EPQ;
-        fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f\n",
-                h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew);
+        fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f (%.0f compactions per CTA)\n",
+                h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
     }
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
     rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, d_idx, d_dist, st);

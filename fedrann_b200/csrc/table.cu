@@ -5,6 +5,8 @@
 // never on the hash function or insertion order.
 #include "common.cuh"
 
+#include <cstdlib>
+
 __global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64_t n, uint4 *slots,
                                        uint32_t *bloom, int lg_cap, int lg_words) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -23,6 +25,42 @@ __global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64
         }
         slot = (slot + 1) & cap_mask;
     }
+}
+
+// every occupied slot's key must be a hash-threshold sample: counters[3] counts the violations
+__global__ void fr_table_verify_sampler_kernel(const uint4 *__restrict__ slots, int64_t cap, int K, uint64_t seed,
+                                               uint64_t threshold, unsigned long long *bad) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = slots[i];
+        const uint64_t key = ((uint64_t)v.y << 32) | v.x;
+        if (key == FR_EMPTY_KEY) continue;
+        uint64_t rc = 0, x = key;
+        for (int j = 0; j < K; ++j) { rc = (rc << 2) | (3ull - (x & 3ull)); x >>= 2; }
+        const uint64_t can = key < rc ? key : rc;
+        if (fr_splitmix64(can ^ seed) >= threshold) atomicAdd(bad, 1ull);
+    }
+}
+
+extern "C" int fr_table_set_sampler(fr_ctx *ctx, uint64_t seed, uint64_t threshold, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    if (!ctx->has_table) return fr_fail(ctx, FR_ERR_STATE, "fr_table_set_sampler: no table");
+    cudaStream_t st = (cudaStream_t)stream;
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    ctx->table.sampled = 0;
+    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 3, 0, sizeof(unsigned long long), st));
+    fr_kt_begin(ctx, "fr_table_verify_sampler_kernel", st);
+    fr_table_verify_sampler_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_slots, 1ll << ctx->table.lg_cap,
+                                                                      ctx->table.k, seed, threshold, ctx->d_counters + 3);
+    FR_LAUNCH_CHECK(ctx, "fr_table_verify_sampler_kernel");
+    FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[3], ctx->d_counters + 3, sizeof(unsigned long long),
+                                 cudaMemcpyDeviceToHost, st));
+    FR_CUDA(ctx, cudaStreamSynchronize(st));
+    if (ctx->h_counters[3] != 0)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_table_set_sampler: the library is not a sample of this sampler");
+    ctx->table.sampled = 1;
+    ctx->table.seed = seed;
+    ctx->table.threshold = threshold;
+    return FR_OK;
 }
 
 static int ceil_log2(int64_t x) {
@@ -45,6 +83,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     int lg_words = ceil_log2(n > 0 ? n : 1);                // 32..64 filter bits per key
     if (lg_words < 8) lg_words = 8;
     if (lg_words > 27) lg_words = 27;
+    if (const char *ov = getenv("FR_BLOOM_LG")) lg_words = atoi(ov);   // timing experiments only
     size_t cap = (size_t)1 << lg_cap, words = (size_t)1 << lg_words;
     if (cudaMalloc(&ctx->d_slots, cap * 16) != cudaSuccess ||
         cudaMalloc(&ctx->d_bloom, words * 4) != cudaSuccess)
@@ -65,6 +104,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     ctx->table.lg_words = lg_words;
     ctx->table.k = k;
     ctx->table.n = n;
+    ctx->table.sampled = 0;
     ctx->has_table = true;
     return FR_OK;
 }

@@ -182,14 +182,25 @@ class Engine:
         return codes[:m].cpu().numpy().view(np.uint64), counts[:m].cpu().numpy().view(np.uint32)
 
     # -- K2 --------------------------------------------------------------
-    def build_table(self, codes, k: int) -> None:
-        """codes: uint64 numpy (or int64-viewed cuda tensor), feature index -> k-mer code."""
+    def build_table(self, codes, k: int, sampler=None) -> None:
+        """codes: uint64 numpy (or int64-viewed cuda tensor), feature index -> k-mer code.
+        sampler = (seed, fraction) declares that the library was sampled by N1's rule
+        (splitmix64(canonical ^ seed) < fraction * 2^64); the claim is verified on the device and
+        `self.sampled` tells whether extraction will use it."""
         if isinstance(codes, np.ndarray):
             codes = self.dev(np.ascontiguousarray(codes, dtype=np.uint64).view(np.int64))
         self._codes = codes
         check(self.h, self.L.fr_table_build(self.h, _ptr(codes), codes.numel(), k, _stream()), "fr_table_build")
         self.k = k
         self.n_features = codes.numel()
+        self.sampled = False
+        if sampler is not None:
+            seed, fraction = sampler
+            thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
+            rc = self.L.fr_table_set_sampler(self.h, seed & (2 ** 64 - 1), thr, _stream())
+            if rc not in (0, -2):
+                check(self.h, rc, "fr_table_set_sampler")
+            self.sampled = rc == 0
 
     # -- K1 + K3 ---------------------------------------------------------
     def extract(self, bases: torch.Tensor, offsets: torch.Tensor, docfreq: torch.Tensor | None = None):

@@ -74,6 +74,14 @@ int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_
 /* d_codes: device u64[n], feature index -> k-mer code, all distinct. */
 int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, int k, void *stream);
 
+/* Optional, after fr_table_build: declare that the library is a hash-threshold sample -- every
+ * key's canonical k-mer c (min of the k-mer and its reverse complement) satisfies
+ * splitmix64(c ^ seed) < threshold, which is how N1 (fr_kmer_count_*) samples.  The claim is
+ * VERIFIED on the device for every key; FR_ERR_ARG (and no change of behaviour) when it does not
+ * hold.  When it holds, extraction rejects positions whose canonical k-mer fails the same test
+ * in registers; results are identical either way. */
+int fr_table_set_sampler(fr_ctx *ctx, uint64_t seed, uint64_t threshold, void *stream);
+
 /* ---- K1+K3: reads -> CSR feature matrix (kmer_searcher.cpp:295-354) ---- */
 /* d_bases: device u8 ASCII, 16-byte aligned, all reads concatenated;
  * d_offsets: device i64[n_reads+1].  Fills d_indptr (i64[n_reads+1]) and, when

@@ -1,7 +1,9 @@
 #!/bin/bash
+# timing experiments on the extract kernel: FR_EXTRACT_DEBUG bits (1 no table probes, 2 no filter loads, 4 no sort), FR_BLOOM_LG
 mkdir -p gpurun_out
-for D in 0 1 2 3 4 7; do
-FR_EXTRACT_DEBUG=$D python - <<'PY'
+for CFG in "0 22" "1 22" "1 20" "1 18" "1 16" "0 20" "0 24" "1 24"; do
+set -- $CFG
+FR_EXTRACT_DEBUG=$1 FR_BLOOM_LG=$2 python - <<'PY'
 import os, torch, numpy as np, sys
 sys.path.insert(0, '.')
 import bench
@@ -15,9 +17,9 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for i in range(3): eng.extract(wl.bases, off)
 eng.profile(True)
 for i in range(5):
-    flush.zero_(); eng.extract(wl.bases, off)
+    flush.zero_(); ip, ix = eng.extract(wl.bases, off)
 torch.cuda.synchronize()
 kt = eng.kernel_times()
-print('dbg', os.environ['FR_EXTRACT_DEBUG'], {k: round(v[1] / v[0], 4) for k, v in kt.items()}, 'maxlen', int(np.diff(wl.offsets).max()))
+print('dbg', os.environ['FR_EXTRACT_DEBUG'], 'bloom_lg', os.environ['FR_BLOOM_LG'], round(kt['fr_extract_kernel'][1] / kt['fr_extract_kernel'][0], 4), 'nnz', ix.numel())
 PY
 done

@@ -205,3 +205,33 @@ def test_normalize_matches_oracle(eng):
     assert np.allclose(norms.cpu().numpy(), on, rtol=1e-6)
     assert Eh.shape == (257, 128) and not Eh[:, 100:].any()
     assert np.allclose(Eh[:, :100].float().cpu().numpy(), Xn, atol=1e-3)
+
+
+@pytest.mark.parametrize("k,fraction", [(15, 0.05), (17, 0.2), (9, 1.0), (31, 0.5), (16, 0.3)])
+def test_extract_sampled_library_fast_path(eng, k, fraction):
+    """A library declared (and verified) as a hash-threshold sample takes the register-only
+    pre-filter; the CSR must equal the generic path's and the oracle's, N/short-read quirks included."""
+    g = S.random_genome(40000, k)
+    rs = S.simulate_reads(g, 8, k, mean_len=2500, len_model="lognormal", min_len=5, sub=0.02, ins=0.01, dele=0.01,
+                          n_frac=0.004)
+    lib = S.library_from_reads(rs, k, fraction, 2, 77)
+    text = lib.searcher_text()
+    from fedrann_b200 import engine
+    codes = engine.parse_library(text, k)
+    ip, ix, _ = O.extract(O.Library(text, k), rs.bases, rs.offsets)
+    b, o = eng.dev(rs.bases), eng.dev(rs.offsets)
+    eng.build_table(codes, k)
+    assert not eng.sampled
+    ip0, ix0 = eng.extract(b, o)
+    eng.build_table(codes, k, sampler=(77, fraction))
+    assert eng.sampled
+    ip1, ix1 = eng.extract(b, o)
+    torch.cuda.synchronize()
+    assert np.array_equal(ip1.cpu().numpy(), ip) and np.array_equal(ix1.cpu().numpy(), ix)
+    assert torch.equal(ip0, ip1) and torch.equal(ix0, ix1)
+    # a wrong claim is detected on the device and ignored
+    if fraction < 1.0:
+        eng.build_table(codes, k, sampler=(78, fraction))
+        assert not eng.sampled
+        ip2, ix2 = eng.extract(b, o)
+        assert torch.equal(ix2, ix1)
