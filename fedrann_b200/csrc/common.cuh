@@ -14,11 +14,16 @@
 // Device-side view of the k-mer lookup structure (K2 builds it, K3 probes it).
 //  * bloom: one-bit-per-key filter, 32-64 bits per key (a false-positive rate of 1.5-3 %), small
 //    enough to stay L2-resident; a probe is ONE 32-byte L2 sector and ~5 instructions.
-//  * slots: open-addressing table of 16-byte slots {key lo, key hi, value, pad} (linear
-//    probing, <= 70 % load) so that a probe that passes the filter costs one sector, too.
+//  * slots: open-addressing table (linear probing, <= 70 % load).  When key and value fit 63
+//    bits together (2k + ceil(log2(F+1)) <= 63: every configuration of the path) a slot is one
+//    packed 64-bit word -- half the footprint, so the table stays L2-resident next to the
+//    streamed reads; otherwise 16-byte slots {key lo, key hi, value, pad}.  Either way a probe
+//    that passes the filter costs one 32-byte sector.
 struct FrTable {
     const uint32_t *bloom;
-    const uint4 *slots;
+    const uint4 *slots;        // wide mode (vbits == 0)
+    const uint64_t *cslots;    // compact mode: (key << vbits) | value in 8 bytes, all-ones = empty
+    int vbits;
     int lg_words;  // log2(#bloom words)
     int lg_cap;    // log2(#table slots)
     int k;
@@ -40,6 +45,7 @@ struct fr_ctx {
     // K2
     uint32_t *d_bloom = nullptr;
     uint4 *d_slots = nullptr;
+    uint64_t *d_cslots = nullptr;
     FrTable table{};
     bool has_table = false;
 

@@ -30,7 +30,7 @@
 #define FR_THREADS 256
 #define FR_PPT 32                       // positions per thread per tile
 #define FR_TILE (FR_THREADS * FR_PPT)   // 8192 positions
-#define FR_QCAP FR_TILE                 // candidate queue (tile positions): a tile can never overflow it
+#define FR_QCAP 2048                    // deferred k-mer queue; drained when a tile might not fit
 #define FR_HCAP 4096                    // shared-memory hit list
 #define FR_NWORDS (FR_TILE / 16 + 2)    // packed words incl. 32 positions of look-behind
 #define FR_MAXB 64                      // most sort buckets (FR_HCAP / 64)
@@ -122,12 +122,14 @@ struct FrExtractShared {
     uint32_t codes[FR_NWORDS];
     uint32_t inv[FR_NWORDS];
     uint32_t rcodes[FR_NWORDS]; // complemented codes, first base least significant (sampled libraries only)
-    uint16_t queue[FR_QCAP];
+    uint64_t kq[FR_QCAP];       // deferred k-mers awaiting their table probe
     int bcnt[FR_MAXB + 1];      // K3c: bucket sizes -> unique counts
     int bstart[FR_MAXB + 1];
     int bfill[FR_MAXB + 1];     // scatter cursors -> output offsets
     int scan[FR_THREADS / 32 + 2];
     int hcount;
+    int qcount;
+    int tcount;                 // survivors of the current tile
     int flag;
     long long misc;
 };
@@ -283,12 +285,11 @@ __device__ __forceinline__ bool fr_kmer_at(const FrExtractShared &sh, int pos, i
     return true;
 }
 
-// append one hit to the read's list; a full list raises sh.flag (the tile is redone after making room)
+// append one hit to the read's list (room was made before the probes were issued)
 __device__ __forceinline__ void fr_append_hit(FrExtractShared &sh, const FrHitList &hl, uint32_t idx) {
     if (hl.dead) return;
     const int pos = atomicAdd(&sh.hcount, 1);
     if (pos < hl.cap) hl.ptr[pos] = idx;
-    else sh.flag = 1;
 }
 
 __device__ __forceinline__ void fr_probe_table(const FrTable &tb, uint64_t kmer, FrExtractShared &sh,
@@ -296,49 +297,114 @@ __device__ __forceinline__ void fr_probe_table(const FrTable &tb, uint64_t kmer,
     const uint32_t cap_mask = (uint32_t)((1ull << tb.lg_cap) - 1);
     uint32_t slot = fr_table_slot(fr_hash(kmer), tb.lg_cap);
     while (true) {
-        const uint4 v = __ldg(&tb.slots[slot]);
-        const uint64_t key = ((uint64_t)v.y << 32) | v.x;
-        if (key == kmer) { fr_append_hit(sh, hl, v.z); return; }
-        if (key == FR_EMPTY_KEY) return;
+        uint64_t key;
+        uint32_t val;
+        if (tb.vbits) {
+            const uint64_t w = __ldg(&tb.cslots[slot]);
+            if (w == FR_EMPTY_KEY) return;
+            key = w >> tb.vbits;
+            val = (uint32_t)(w & ((1ull << tb.vbits) - 1));
+        } else {
+            const uint4 v = __ldg(&tb.slots[slot]);
+            key = ((uint64_t)v.y << 32) | v.x;
+            if (key == FR_EMPTY_KEY) return;
+            val = v.z;
+        }
+        if (key == kmer) { fr_append_hit(sh, hl, val); return; }
         slot = (slot + 1) & cap_mask;
     }
 }
 
-// K3b: one warp drains its own survivors (tile positions wq[0..n)) against the table.  The
-// first slot of FR_NB candidates per lane is requested before any is examined: a probe is a
-// random DRAM/L2 access and only the number of them in flight matters.
+// Makes room for `n` more hits (block-uniform): sort + unique of what is there, and if that is
+// not enough the list moves to a global slab that can hold one entry per lookup of the read.
+__device__ void fr_make_room(FrExtractShared &sh, FrHitList &hl, int n, int64_t n_lookups, uint32_t *spill,
+                             int64_t spill_cap, unsigned long long *counters) {
+    int hc = sh.hcount;
+    __syncthreads();
+    if (hc + n <= hl.cap || hl.dead) return;
+    const int u = fr_block_sort_unique(hl.ptr, hc, sh.scan);
+    if (threadIdx.x == 0) sh.hcount = u;
+    __syncthreads();
+    hc = u;
+    if (hc + n <= hl.cap) return;
+    long long need = 1;
+    while (need < n_lookups) need <<= 1;
+    if (threadIdx.x == 0) sh.misc = (long long)atomicAdd(&counters[1], (unsigned long long)need);
+    __syncthreads();
+    const long long off = sh.misc;
+    if (off + need > spill_cap) {
+        if (threadIdx.x == 0) atomicOr(&counters[2], FR_FLAG_SPILL_OVERFLOW);
+        hl.dead = true;
+    } else {
+        uint32_t *dst = spill + off;
+        for (int i = threadIdx.x; i < hc; i += FR_THREADS) dst[i] = hl.ptr[i];
+        hl.ptr = dst;
+        hl.cap = (int)(need > 0x40000000ll ? 0x40000000ll : need);
+    }
+    __syncthreads();
+}
+
+// K3b: the block drains the deferred k-mer queue against the table.  The first slot of FR_NB
+// k-mers per thread is requested before any is examined: a probe is a random DRAM/L2 access and
+// only the number of them in flight matters.
 #define FR_NB 4
-__device__ __forceinline__ void fr_warp_drain(FrExtractShared &sh, const FrHitList &hl, const FrTable &tb,
-                                              const uint16_t *wq, int n, int lane, uint64_t kmask) {
+__device__ void fr_block_drain(FrExtractShared &sh, FrHitList &hl, const FrTable &tb, int64_t n_lookups,
+                               uint32_t *spill, int64_t spill_cap, unsigned long long *counters) {
+    const int n = sh.qcount;
+    __syncthreads();
+    if (n == 0) return;
+    fr_make_room(sh, hl, n, n_lookups, spill, spill_cap, counters);
     const uint32_t cap_mask = (uint32_t)((1ull << tb.lg_cap) - 1);
-    for (int i0 = 0; i0 < n; i0 += 32 * FR_NB) {
+    const int vb = tb.vbits;
+    const uint64_t vmask = (1ull << vb) - 1;
+    for (int i0 = 0; i0 < n; i0 += FR_THREADS * FR_NB) {
         uint64_t km[FR_NB];
         uint32_t slot[FR_NB];
-        uint4 v[FR_NB];
         bool ok[FR_NB];
 #pragma unroll
         for (int b = 0; b < FR_NB; ++b) {
-            const int i = i0 + 32 * b + lane;
-            km[b] = 0;
-            ok[b] = i < n && fr_kmer_at(sh, wq[i], tb.k, kmask, km[b]);
+            const int i = i0 + FR_THREADS * b + threadIdx.x;
+            ok[b] = i < n;
+            km[b] = ok[b] ? sh.kq[i] : 0ull;
+            ok[b] = ok[b] && km[b] != FR_EMPTY_KEY;
             slot[b] = fr_table_slot(fr_hash(km[b]), tb.lg_cap);
         }
+        if (vb) {
+            uint64_t w[FR_NB];
 #pragma unroll
-        for (int b = 0; b < FR_NB; ++b) v[b] = ok[b] ? __ldg(&tb.slots[slot[b]]) : make_uint4(0, 0, 0, 0);
+            for (int b = 0; b < FR_NB; ++b) w[b] = ok[b] ? __ldg(&tb.cslots[slot[b]]) : FR_EMPTY_KEY;
 #pragma unroll
-        for (int b = 0; b < FR_NB; ++b) {
-            if (!ok[b]) continue;
-            uint4 w = v[b];
-            uint32_t sl = slot[b];
-            while (true) {
-                const uint64_t key = ((uint64_t)w.y << 32) | w.x;
-                if (key == km[b]) { fr_append_hit(sh, hl, w.z); break; }
-                if (key == FR_EMPTY_KEY) break;
-                sl = (sl + 1) & cap_mask;
-                w = __ldg(&tb.slots[sl]);
+            for (int b = 0; b < FR_NB; ++b) {
+                uint64_t x = w[b];
+                uint32_t sl = slot[b];
+                while (x != FR_EMPTY_KEY) {
+                    if ((x >> vb) == km[b]) { fr_append_hit(sh, hl, (uint32_t)(x & vmask)); break; }
+                    sl = (sl + 1) & cap_mask;
+                    x = __ldg(&tb.cslots[sl]);
+                }
+            }
+        } else {
+            uint4 v[FR_NB];
+#pragma unroll
+            for (int b = 0; b < FR_NB; ++b) v[b] = ok[b] ? __ldg(&tb.slots[slot[b]]) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int b = 0; b < FR_NB; ++b) {
+                if (!ok[b]) continue;
+                uint4 w = v[b];
+                uint32_t sl = slot[b];
+                while (true) {
+                    const uint64_t key = ((uint64_t)w.y << 32) | w.x;
+                    if (key == km[b]) { fr_append_hit(sh, hl, w.z); break; }
+                    if (key == FR_EMPTY_KEY) break;
+                    sl = (sl + 1) & cap_mask;
+                    w = __ldg(&tb.slots[sl]);
+                }
             }
         }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) sh.qcount = 0;
+    __syncthreads();
 }
 
 // K3a for one thread: 32 filter probes, all independent.  c0..c3 = packed codes of the 32
@@ -432,15 +498,13 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
         const int64_t lo = len >= K ? s + K - 1 : e - 1;  // first lookup position
         FrHitList hl;
         hl.ptr = sh.hits; hl.cap = FR_HCAP; hl.dead = false;
-        if (tid == 0) { sh.hcount = 0; sh.flag = 0; }
+        if (tid == 0) { sh.hcount = 0; sh.flag = 0; sh.qcount = 0; sh.tcount = 0; }
         __syncthreads();
         if (len == 0 && tid == 0) fr_probe_table(tb, 0ull, sh, hl);   // kmer_searcher.cpp:325 with an empty read
         const int64_t abase = s & ~15ll;
         const int64_t ntiles = len > 0 ? (e - abase + FR_TILE - 1) / FR_TILE : 0;
-        bool compacted = false;     // this tile was already retried after a compaction
         for (int64_t tile = 0; tile < ntiles; ++tile) {
             const int64_t tile_start = abase + tile * FR_TILE;
-            const int hc0 = sh.hcount;      // uniform: a barrier precedes every iteration
             // ---- K1: pack this tile (plus 32 positions of look-behind); bases outside the read are A, valid ----
             for (int w = tid; w < FR_NWORDS; w += FR_THREADS) {
                 const int64_t g = tile_start - 32 + 16ll * w;
@@ -448,7 +512,7 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 if (g + 16 > s && g < e) {
                     uint4 v;
                     if (g >= 0 && g + 16 <= n_bases) {
-                        v = __ldg(reinterpret_cast<const uint4 *>(bases + g));
+                        v = __ldcs(reinterpret_cast<const uint4 *>(bases + g));   // streamed once: evict first
                     } else {
                         uint32_t b[4] = {0, 0, 0, 0};
                         for (int j = 0; j < 16; ++j) {
@@ -503,53 +567,45 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 pass = (pass & pm & ~am) | (pm & am & ~(uint32_t)iv64);
                 if (dbg & 1) pass = 0;
             }
-            // ---- K3b: the warp queues its survivors' tile positions and drains them ----
+            // ---- K3b: survivors are rebuilt as k-mers and deferred; the block probes the table in bulk ----
             {
-                uint16_t *wq = sh.queue + (tid >> 5) * (32 * FR_PPT);
                 int total;
                 int my = fr_warp_excl_scan(__popc(pass), lane, total);
-                if (total) {
+                if (lane == 31 && total) atomicAdd(&sh.tcount, total);
+                __syncthreads();
+                const int tcount = sh.tcount, qc0 = sh.qcount;
+                __syncthreads();                            // everyone holds the same counts before they move
+                if (qc0 + tcount > FR_QCAP) {               // uniform: make the queue empty first
+                    fr_block_drain(sh, hl, tb, n_lookups, spill, spill_cap, counters);
+                }
+                if (tcount <= FR_QCAP) {
+                    int base = 0;
+                    if (lane == 31 && total) base = atomicAdd(&sh.qcount, total);
+                    my += __shfl_sync(0xFFFFFFFFu, base, 31);
                     while (pass) {
                         const int j = __clz(pass);
-                        wq[my++] = (uint16_t)(FR_PPT * tid + j);
                         pass &= ~(0x80000000u >> j);
+                        uint64_t kmer;
+                        // a position whose own base is not ACGT was never selected, so this cannot fail;
+                        // the slot is filled either way to keep the queue dense
+                        if (!fr_kmer_at(sh, FR_PPT * tid + j, K, kmask, kmer)) kmer = FR_EMPTY_KEY;
+                        sh.kq[my++] = kmer;
                     }
-                    __syncwarp();
-                    fr_warp_drain(sh, hl, tb, wq, total, lane, kmask);
-                }
-            }
-            __syncthreads();
-            if (sh.flag) {
-                // the hit list filled up: drop this tile's hits, make room, run the tile again
-                __syncthreads();
-                if (!compacted) {
-                    const int u = fr_block_sort_unique(hl.ptr, hc0, sh.scan);
-                    if (tid == 0) { sh.hcount = u; sh.flag = 0; }
-                    compacted = true;
                 } else {
-                    // migrate to a global slab that can hold one entry per lookup position
-                    long long need = 1;
-                    while (need < n_lookups) need <<= 1;
-                    if (tid == 0) sh.misc = (long long)atomicAdd(&counters[1], (unsigned long long)need);
-                    __syncthreads();
-                    const long long off = sh.misc;
-                    if (off + need > spill_cap) {
-                        if (tid == 0) atomicOr(&counters[2], FR_FLAG_SPILL_OVERFLOW);
-                        hl.dead = true;
-                    } else {
-                        uint32_t *dst = spill + off;
-                        for (int i = tid; i < hc0; i += FR_THREADS) dst[i] = hl.ptr[i];
-                        hl.ptr = dst;
-                        hl.cap = (int)(need > 0x40000000ll ? 0x40000000ll : need);
+                    // a tile with more survivors than the queue holds (dense libraries): probe directly
+                    fr_make_room(sh, hl, tcount, n_lookups, spill, spill_cap, counters);
+                    while (pass) {
+                        const int j = __clz(pass);
+                        pass &= ~(0x80000000u >> j);
+                        uint64_t kmer;
+                        if (fr_kmer_at(sh, FR_PPT * tid + j, K, kmask, kmer)) fr_probe_table(tb, kmer, sh, hl);
                     }
-                    if (tid == 0) { sh.hcount = hc0; sh.flag = 0; }
                 }
-                __syncthreads();
-                --tile;
-                continue;
             }
-            compacted = false;
+            __syncthreads();                                 // sh.codes may be overwritten now
+            if (tid == 0) sh.tcount = 0;
         }
+        fr_block_drain(sh, hl, tb, n_lookups, spill, spill_cap, counters);
         // ---- K3c: sort + unique, emit ----
         __syncthreads();
         int u = -1;

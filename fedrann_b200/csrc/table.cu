@@ -7,6 +7,28 @@
 
 #include <cstdlib>
 
+__global__ void fr_table_insert_compact_kernel(const uint64_t *__restrict__ codes, int64_t n,
+                                               unsigned long long *cslots, uint32_t *bloom, int lg_cap,
+                                               int lg_words, int vbits) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t key = codes[i];
+    const uint32_t bh = fr_bloom_hash((uint32_t)key, (uint32_t)(key >> 32));
+    atomicOr(&bloom[fr_bloom_word(bh, lg_words)], 0x80000000u >> fr_bloom_shift(bh, lg_words));
+    const uint32_t cap_mask = (uint32_t)((1ull << lg_cap) - 1);
+    uint32_t slot = fr_table_slot(fr_hash(key), lg_cap);
+    const unsigned long long mine = (key << vbits) | (unsigned long long)i;
+    while (true) {
+        unsigned long long old = atomicCAS(&cslots[slot], (unsigned long long)FR_EMPTY_KEY, mine);
+        if (old == FR_EMPTY_KEY) return;
+        if ((old >> vbits) == key) {                 // duplicates keep the first occurrence
+            atomicMin(&cslots[slot], mine);
+            return;
+        }
+        slot = (slot + 1) & cap_mask;
+    }
+}
+
 __global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64_t n, uint4 *slots,
                                        uint32_t *bloom, int lg_cap, int lg_words) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -28,12 +50,20 @@ __global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64
 }
 
 // every occupied slot's key must be a hash-threshold sample: counters[3] counts the violations
-__global__ void fr_table_verify_sampler_kernel(const uint4 *__restrict__ slots, int64_t cap, int K, uint64_t seed,
-                                               uint64_t threshold, unsigned long long *bad) {
+__global__ void fr_table_verify_sampler_kernel(const uint4 *__restrict__ slots, const uint64_t *__restrict__ cslots,
+                                               int vbits, int64_t cap, int K, uint64_t seed, uint64_t threshold,
+                                               unsigned long long *bad) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (int64_t)gridDim.x * blockDim.x) {
-        const uint4 v = slots[i];
-        const uint64_t key = ((uint64_t)v.y << 32) | v.x;
-        if (key == FR_EMPTY_KEY) continue;
+        uint64_t key;
+        if (vbits) {
+            const uint64_t w = cslots[i];
+            if (w == FR_EMPTY_KEY) continue;
+            key = w >> vbits;
+        } else {
+            const uint4 v = slots[i];
+            key = ((uint64_t)v.y << 32) | v.x;
+            if (key == FR_EMPTY_KEY) continue;
+        }
         uint64_t rc = 0, x = key;
         for (int j = 0; j < K; ++j) { rc = (rc << 2) | (3ull - (x & 3ull)); x >>= 2; }
         const uint64_t can = key < rc ? key : rc;
@@ -49,8 +79,9 @@ extern "C" int fr_table_set_sampler(fr_ctx *ctx, uint64_t seed, uint64_t thresho
     ctx->table.sampled = 0;
     FR_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 3, 0, sizeof(unsigned long long), st));
     fr_kt_begin(ctx, "fr_table_verify_sampler_kernel", st);
-    fr_table_verify_sampler_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_slots, 1ll << ctx->table.lg_cap,
-                                                                      ctx->table.k, seed, threshold, ctx->d_counters + 3);
+    fr_table_verify_sampler_kernel<<<ctx->sm_count * 8, 256, 0, st>>>(ctx->d_slots, ctx->d_cslots, ctx->table.vbits,
+                                                                      1ll << ctx->table.lg_cap, ctx->table.k, seed,
+                                                                      threshold, ctx->d_counters + 3);
     FR_LAUNCH_CHECK(ctx, "fr_table_verify_sampler_kernel");
     FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[3], ctx->d_counters + 3, sizeof(unsigned long long),
                                  cudaMemcpyDeviceToHost, st));
@@ -77,6 +108,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     FR_CUDA(ctx, cudaSetDevice(ctx->device));
     if (ctx->d_bloom) { cudaFree(ctx->d_bloom); ctx->d_bloom = nullptr; }
     if (ctx->d_slots) { cudaFree(ctx->d_slots); ctx->d_slots = nullptr; }
+    if (ctx->d_cslots) { cudaFree(ctx->d_cslots); ctx->d_cslots = nullptr; }
     ctx->has_table = false;
     int lg_cap = ceil_log2(n > 0 ? (n * 10 + 6) / 7 : 1);   // load <= 0.7
     if (lg_cap < 10) lg_cap = 10;
@@ -85,19 +117,29 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     if (lg_words > 27) lg_words = 27;
     if (const char *ov = getenv("FR_BLOOM_LG")) lg_words = atoi(ov);   // timing experiments only
     size_t cap = (size_t)1 << lg_cap, words = (size_t)1 << lg_words;
-    if (cudaMalloc(&ctx->d_slots, cap * 16) != cudaSuccess ||
-        cudaMalloc(&ctx->d_bloom, words * 4) != cudaSuccess)
+    int vbits = ceil_log2(n + 2);                           // values 0..n-1 never read as all-ones
+    if (vbits < 1) vbits = 1;
+    if (2 * k + vbits > 63 || getenv("FR_TABLE_WIDE")) vbits = 0;   // wide slots
+    if (cudaMalloc(&ctx->d_bloom, words * 4) != cudaSuccess ||
+        (vbits ? cudaMalloc(&ctx->d_cslots, cap * 8) : cudaMalloc(&ctx->d_slots, cap * 16)) != cudaSuccess)
         return fr_fail(ctx, FR_ERR_NOMEM, "fr_table_build: cudaMalloc failed");
-    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_slots, 0xFF, cap * 16, st));
+    if (vbits) FR_CUDA(ctx, cudaMemsetAsync(ctx->d_cslots, 0xFF, cap * 8, st));
+    else FR_CUDA(ctx, cudaMemsetAsync(ctx->d_slots, 0xFF, cap * 16, st));
     FR_CUDA(ctx, cudaMemsetAsync(ctx->d_bloom, 0, words * 4, st));
     if (n > 0) {
         int threads = 256;
         int64_t blocks = (n + threads - 1) / threads;
         fr_kt_begin(ctx, "fr_table_insert_kernel", st);
-        fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_slots, ctx->d_bloom,
-                                                                      lg_cap, lg_words);
+        if (vbits)
+            fr_table_insert_compact_kernel<<<(unsigned)blocks, threads, 0, st>>>(
+                d_codes, n, (unsigned long long *)ctx->d_cslots, ctx->d_bloom, lg_cap, lg_words, vbits);
+        else
+            fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_slots, ctx->d_bloom,
+                                                                          lg_cap, lg_words);
         FR_LAUNCH_CHECK(ctx, "fr_table_insert_kernel");
     }
+    ctx->table.cslots = ctx->d_cslots;
+    ctx->table.vbits = vbits;
     ctx->table.bloom = ctx->d_bloom;
     ctx->table.slots = ctx->d_slots;
     ctx->table.lg_cap = lg_cap;
