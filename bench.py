@@ -369,7 +369,15 @@ def main():
 
     # ---- roofline of the dominant kernel (largest share of the device-timed step on this rank)
     peaks = measured_peaks()
-    roof = roofline(ktimes, args.steps, wl, res, w, world_eff, peaks, args.ncu_traffic, ms_per_step)
+    traffic = args.ncu_traffic
+    if traffic is None and args.workload == "c2" and world == 1:
+        # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed
+        # `ncu --set full` capture of this workload (profiles/ncu_traffic.json)
+        tp = join(ROOT, "profiles", "ncu_traffic.json")
+        if isfile(tp) and ktimes:
+            top = max(ktimes, key=lambda k: ktimes[k][1])
+            traffic = json.load(open(tp)).get(top, {}).get("dram_bytes_per_launch")
+    roof = roofline(ktimes, args.steps, wl, res, w, world_eff, peaks, traffic, ms_per_step)
 
     # ---- CPU baseline (rank 0, N=1 only)
     cpu = None

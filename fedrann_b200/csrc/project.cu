@@ -13,7 +13,8 @@
 // reverse row, each in its own D-float shared-memory accumulator.
 #include "common.cuh"
 
-#define FR_PJ_STAGE 256
+#define FR_PJ_STAGE 512
+#define FR_PJ_U 4
 
 __device__ __forceinline__ void fr_apply_group(float *acc, int j, float v, bool valid) {
     // lanes with equal j must add in lane order
@@ -44,47 +45,52 @@ fr_project_kernel(const int64_t *__restrict__ indptr, const int32_t *__restrict_
         const int64_t a = indptr[r];
         const int n = (int)(indptr[r + 1] - a);
         const int32_t *row = indices + a;
-        // split = number of hits < nk (row is ascending): binary search, all lanes alike
+        // split = number of hits < nk (the row is ascending): counted with coalesced loads (one
+        // round trip instead of a dependent binary search; the row is then in L1 for the passes below)
         int split = 0;
-        {
-            int lo = 0, hi = n;
-            while (lo < hi) {
-                int mid = (lo + hi) >> 1;
-                if ((int64_t)row[mid] < nk) lo = mid + 1; else hi = mid;
-            }
-            split = lo;
-        }
-        for (int base = 0; base < n; base += 32) {
-            const int t = base + lane;
-            const bool valid = t < n;
-            int64_t feat = 0;
-            if (valid) {
-                if (warp == 0) {
-                    feat = row[t];
-                } else {  // swapped set in ascending order: [hits >= nk] - nk, then [hits < nk] + nk
-                    const int nhi = n - split;
-                    feat = t < nhi ? (int64_t)row[split + t] - nk : (int64_t)row[t - nhi] + nk;
+        for (int t = lane; t < n; t += 32) split += (int64_t)row[t] < nk;
+        split = __reduce_add_sync(0xFFFFFFFFu, split);
+        const int nhi = n - split;
+        // FR_PJ_U groups of 32 hits per pass: their P.indptr lookups and P entries are independent
+        // loads, so the three dependent round trips (hit -> indptr -> entries) are paid once per 128 hits
+        for (int base = 0; base < n; base += 32 * FR_PJ_U) {
+            int64_t pa[FR_PJ_U];
+            int cnt[FR_PJ_U], excl[FR_PJ_U];
+#pragma unroll
+            for (int u = 0; u < FR_PJ_U; ++u) {
+                const int t = base + 32 * u + lane;
+                int64_t feat = -1;
+                if (t < n) {
+                    if (warp == 0) feat = row[t];
+                    else  // swapped set in ascending order: [hits >= nk] - nk, then [hits < nk] + nk
+                        feat = t < nhi ? (int64_t)row[split + t] - nk : (int64_t)row[t - nhi] + nk;
+                }
+                pa[u] = 0;
+                cnt[u] = 0;
+                if (feat >= 0) {
+                    pa[u] = __ldg(&p_indptr[feat]);
+                    cnt[u] = (int)(__ldg(&p_indptr[feat + 1]) - pa[u]);
                 }
             }
-            int64_t pa = 0;
-            int cnt = 0;
-            if (valid) {
-                pa = __ldg(&p_indptr[feat]);
-                cnt = (int)(__ldg(&p_indptr[feat + 1]) - pa);
+            int total = 0;
+#pragma unroll
+            for (int u = 0; u < FR_PJ_U; ++u) {     // staging order = hit order: group u, then lane
+                int incl = cnt[u];
+                for (int d = 1; d < 32; d <<= 1) {
+                    int y = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                    if (lane >= d) incl += y;
+                }
+                excl[u] = total + incl - cnt[u];
+                total += __shfl_sync(0xFFFFFFFFu, incl, 31);
             }
-            int incl = cnt;
-            for (int d = 1; d < 32; d <<= 1) {
-                int y = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-                if (lane >= d) incl += y;
-            }
-            const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-            const int excl = incl - cnt;
             if (total == 0) continue;
             if (total <= FR_PJ_STAGE) {
-                for (int m = 0; m < cnt; ++m) {
-                    st_col[excl + m] = __ldg(&p_indices[pa + m]);
-                    st_val[excl + m] = __ldg(&p_data[pa + m]);
-                }
+#pragma unroll
+                for (int u = 0; u < FR_PJ_U; ++u)
+                    for (int m = 0; m < cnt[u]; ++m) {
+                        st_col[excl[u] + m] = __ldg(&p_indices[pa[u] + m]);
+                        st_val[excl[u] + m] = __ldg(&p_data[pa[u] + m]);
+                    }
                 __syncwarp();
                 for (int g = 0; g < total; g += 32) {
                     const int e = g + lane;
@@ -95,15 +101,17 @@ fr_project_kernel(const int64_t *__restrict__ indptr, const int32_t *__restrict_
                 }
                 __syncwarp();
             } else {
-                // pathological density: strictly sequential, lane by lane
-                for (int l = 0; l < 32; ++l) {
-                    if (lane == l)
-                        for (int m = 0; m < cnt; ++m) {
-                            int j = __ldg(&p_indices[pa + m]);
-                            acc[j] = __fadd_rn(acc[j], __ldg(&p_data[pa + m]));
-                        }
-                    __syncwarp();
-                }
+                // pathological density: strictly sequential, group by group, lane by lane
+#pragma unroll
+                for (int u = 0; u < FR_PJ_U; ++u)
+                    for (int l = 0; l < 32; ++l) {
+                        if (lane == l)
+                            for (int m = 0; m < cnt[u]; ++m) {
+                                int j = __ldg(&p_indices[pa[u] + m]);
+                                acc[j] = __fadd_rn(acc[j], __ldg(&p_data[pa[u] + m]));
+                            }
+                        __syncwarp();
+                    }
             }
         }
         __syncwarp();

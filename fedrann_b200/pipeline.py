@@ -106,17 +106,74 @@ class HostBuffers:
 
 
 def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *, mode: int = 0, group=None,
-                      timers: StageTimes | None = None) -> HotPathResult:
+                      timers: StageTimes | None = None, chunks: int = 8) -> HotPathResult:
     """The call a host program makes: reads in pinned host memory -> device ->
     extract/project/kNN -> neighbour lists back in pinned host memory.  Returns
-    after the results have landed."""
+    after the results have landed.
+
+    The reads cross PCIe in `chunks` pieces on a copy stream while the compute
+    stream extracts and projects the pieces that have arrived (reads are
+    independent); the kNN starts when the last piece is projected."""
     dev = torch.device("cuda", eng.device)
     n = hb.bases.numel()
+    R = hb.offsets.numel() - 1
+    cur = torch.cuda.current_stream()
+    copy_stream = _copy_stream(dev)
     bases_d = torch.empty(n + 16, dtype=torch.uint8, device=dev)[:n]
-    bases_d.copy_(hb.bases, non_blocking=True)
     offsets_d = hb.offsets.to(dev, non_blocking=True)
-    res = run_hot_path(eng, bases_d, offsets_d, P_dev, nk, k_nn, mode=mode, timers=timers, group=group)
+    chunks = max(1, min(chunks, R))
+    # read ranges balanced by bases
+    off = hb.offsets
+    bounds = [0]
+    for c in range(1, chunks):
+        target = int(off[0]) + (n * c) // chunks
+        bounds.append(max(bounds[-1], int(torch.searchsorted(off, torch.tensor(target)).item())))
+    bounds.append(R)
+    copy_stream.wait_stream(cur)
+    events = []
+    with torch.cuda.stream(copy_stream):
+        for c in range(chunks):
+            b0, b1 = int(off[bounds[c]]), int(off[bounds[c + 1]])
+            if b1 > b0:
+                bases_d[b0:b1].copy_(hb.bases[b0:b1], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+            events.append(ev)
+    D = P_dev[3]
+    E = torch.empty((2 * R, D), dtype=torch.float32, device=dev)
+    ips, ixs, base = [], [], 0
+    for c in range(chunks):
+        r0, r1 = bounds[c], bounds[c + 1]
+        cur.wait_event(events[c])
+        if r1 == r0:
+            continue
+        ip, ix = eng.extract(bases_d, offsets_d[r0:r1 + 1])
+        eng.project(ip, ix, P_dev, nk, out=E[2 * r0:2 * r1])
+        ips.append(ip[1:] + base if ips else ip)
+        ixs.append(ix)
+        base += int(ix.numel())
+    bases_d.record_stream(copy_stream)
+    indptr = torch.cat(ips) if ips else torch.zeros(1, dtype=torch.int64, device=dev)
+    indices = torch.cat(ixs) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
+    En, Eh, norms = eng.normalize(E)
+    q0, nq = 0, En.shape[0]
+    if group is not None and torch.distributed.get_world_size(group) > 1:
+        from .parallel import all_gather_rows
+        En, Eh, norms, q0 = all_gather_rows(En, Eh, norms, group)
+    k_eff = min(k_nn, En.shape[0])
+    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode)
+    res = HotPathResult(indptr, indices, E, idx, dist, q0)
     hb.nbr_idx[:, : res.nbr_idx.shape[1]].copy_(res.nbr_idx, non_blocking=True)
     hb.nbr_dist[:, : res.nbr_dist.shape[1]].copy_(res.nbr_dist, non_blocking=True)
     torch.cuda.current_stream().synchronize()
     return res
+
+
+_copy_streams: dict = {}
+
+
+def _copy_stream(dev):
+    s = _copy_streams.get(dev.index)
+    if s is None:
+        s = _copy_streams[dev.index] = torch.cuda.Stream(device=dev)
+    return s

@@ -235,3 +235,26 @@ def test_extract_sampled_library_fast_path(eng, k, fraction):
         assert not eng.sampled
         ip2, ix2 = eng.extract(b, o)
         assert torch.equal(ix2, ix1)
+
+
+def test_host_path_chunked_equals_device_path(eng):
+    """run_hot_path_host (reads cross PCIe in pieces, overlapped with extract/project) returns what
+    run_hot_path returns on device-resident reads."""
+    from fedrann_b200.pipeline import HostBuffers, run_hot_path, run_hot_path_host
+    from fedrann_b200.precompute import precompute_matrix
+    k, D, knn_k = 15, 64, 10
+    g = S.random_genome(80000, 21)
+    rs = S.simulate_reads(g, 12, 21, mean_len=3000, len_model="lognormal", min_len=30, sub=0.02, ins=0.01, dele=0.01,
+                          n_frac=0.002)
+    lib = S.library_from_reads(rs, k, 0.05, 2, 21)
+    eng.build_table(lib.all_codes(), k, sampler=(21, 0.05))
+    P_dev = eng.upload_projection(precompute_matrix(D, lib.counts, lib.n_features))
+    bases_d, offs_d = eng.dev(rs.bases), eng.dev(rs.offsets)
+    a = run_hot_path(eng, bases_d, offs_d, P_dev, lib.nk, knn_k)
+    hb = HostBuffers.from_device(bases_d, rs.offsets, 2 * rs.n_reads, knn_k)
+    for chunks in (1, 3, 8, 1000):
+        b = run_hot_path_host(eng, hb, P_dev, lib.nk, knn_k, chunks=chunks)
+        assert torch.equal(a.indptr, b.indptr) and torch.equal(a.indices, b.indices)
+        assert torch.equal(a.embedding, b.embedding)
+        assert torch.equal(a.nbr_idx, b.nbr_idx) and torch.equal(a.nbr_dist, b.nbr_dist)
+        assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu()) and torch.equal(hb.nbr_dist, a.nbr_dist.cpu())
