@@ -120,7 +120,7 @@ extern "C" void fr_destroy(fr_ctx *ctx) {
     cudaFree(ctx->d_bloom); cudaFree(ctx->d_slots); cudaFree(ctx->d_cslots);
     cudaFree(ctx->d_scratch); cudaFree(ctx->d_spill); cudaFree(ctx->d_read_off);
     cudaFree(ctx->d_read_cnt); cudaFree(ctx->d_counters); cudaFree(ctx->d_scan_tmp);
-    cudaFree(ctx->d_knn_ws); cudaFree(ctx->d_count_slots);
+    cudaFree(ctx->d_knn_ws); cudaFree(ctx->d_knn_fb); cudaFree(ctx->d_count_slots);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     fr_kt_clear(ctx);
     delete ctx;

@@ -81,6 +81,8 @@ struct fr_ctx {
     // K6/K7 scratch
     void *d_knn_ws = nullptr;
     int64_t knn_ws_cap = 0;
+    void *d_knn_fb = nullptr;       // exact distances of the fallback rows (parallel fallback)
+    int64_t knn_fb_cap = 0;
     int64_t knn_fallback_rows = 0;
     bool knn_fb_pending = false;    // h_counters[4] holds the count once knn_fb_stream has drained
     cudaStream_t knn_fb_stream = nullptr;

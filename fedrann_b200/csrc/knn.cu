@@ -5,7 +5,7 @@
 
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
-                        int32_t *d_idx, float *d_dist, cudaStream_t st);
+                        int64_t row_skip, int32_t *d_idx, float *d_dist, cudaStream_t st);
 int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
                      int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st);
 
@@ -21,7 +21,7 @@ extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const fl
     ctx->knn_fb_pending = false;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == 1)
-        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
+        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     if (mode != 0) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode must be 0 or 1");
     if (!d_Eh || Dp < D || (Dp % 64) != 0)
         return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode 0 needs the fp16 copy with Dp % 64 == 0");

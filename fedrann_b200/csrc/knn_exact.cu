@@ -78,7 +78,7 @@ __device__ __forceinline__ void fr_list_insert(float *ld, int *li, int k, float 
 __global__ void __launch_bounds__(FR_EX_WARPS * 32)
 fr_knn_exact_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D,
                     int64_t q0, int64_t nq, int k, const int32_t *__restrict__ rows,
-                    const unsigned long long *__restrict__ n_rows, int32_t *__restrict__ out_idx,
+                    const unsigned long long *__restrict__ n_rows, int64_t row_skip, int32_t *__restrict__ out_idx,
                     float *__restrict__ out_dist) {
     extern __shared__ __align__(16) unsigned char fr_ex_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -88,7 +88,9 @@ fr_knn_exact_kernel(const float *__restrict__ En, const float *__restrict__ norm
     int *li = reinterpret_cast<int *>(reinterpret_cast<float *>(fr_ex_smem) + (size_t)FR_EX_WARPS * FR_QPW * D +
                                       (size_t)FR_EX_WARPS * FR_QPW * FR_MAX_K) +
               (size_t)warp * FR_QPW * FR_MAX_K;
-    const int64_t total = rows ? (int64_t)(*n_rows) : nq;
+    // with a row list the first row_skip entries were answered by the parallel fallback below
+    const int64_t total = rows ? ((int64_t)(*n_rows) > row_skip ? (int64_t)(*n_rows) - row_skip : 0) : nq;
+    if (rows) rows += row_skip;
     const int64_t ngroups = (total + FR_QPW - 1) / FR_QPW;
     for (int64_t g = (int64_t)blockIdx.x * FR_EX_WARPS + warp; g < ngroups; g += (int64_t)gridDim.x * FR_EX_WARPS) {
         int64_t qloc[FR_QPW];
@@ -142,7 +144,7 @@ fr_knn_exact_kernel(const float *__restrict__ En, const float *__restrict__ norm
 
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
-                        int32_t *d_idx, float *d_dist, cudaStream_t st) {
+                        int64_t row_skip, int32_t *d_idx, float *d_dist, cudaStream_t st) {
     if (k < 1 || k > FR_MAX_K) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: k must be in [1,128]");
     size_t smem = (size_t)FR_EX_WARPS * FR_QPW * D * sizeof(float) +
                   (size_t)FR_EX_WARPS * FR_QPW * FR_MAX_K * (sizeof(float) + sizeof(int));
@@ -154,7 +156,154 @@ int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, in
     if (blocks < 1) blocks = 1;
     fr_kt_begin(ctx, "fr_knn_exact_kernel", st);
     fr_knn_exact_kernel<<<(unsigned)blocks, FR_EX_WARPS * 32, smem, st>>>(d_En, d_norms, n_db, D, q0, nq, k, d_rows,
-                                                                          d_n_rows, d_idx, d_dist);
+                                                                          d_n_rows, row_skip, d_idx, d_dist);
     FR_LAUNCH_CHECK(ctx, "fr_knn_exact_kernel");
+    return FR_OK;
+}
+
+// ---- parallel fallback for the few rows the tensor-core path could not certify ----
+// Same arithmetic as the scan above (lane-strided FMA, xor-shuffle reduction), organised the
+// other way round: one warp per DATABASE row computes the exact distance of every fallback
+// query (their rows sit in shared memory) and stores orderable 64-bit keys (distance, index);
+// then one CTA per query finds its k smallest keys exactly -- a bitwise binary search for the
+// k-th smallest key over the whole key array, a gather of the k keys at or below it, a sort.
+#define FR_FB_MAX 32        // queries answered per launch (the rest take the scan above)
+#define FR_FB_QB 8          // queries per block of the distance kernel
+
+__device__ __forceinline__ uint32_t fr_f2ord(float f) {
+    uint32_t u = __float_as_uint(f);
+    return u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);
+}
+__device__ __forceinline__ float fr_ord2f(uint32_t u) {
+    return __uint_as_float(u ^ ((u >> 31) ? 0x80000000u : 0xFFFFFFFFu));
+}
+
+__global__ void __launch_bounds__(256)
+fr_knn_fb_dist_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
+                      const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int fb_max,
+                      unsigned long long *__restrict__ keys) {
+    extern __shared__ __align__(16) unsigned char fr_fb_smem[];
+    float *qbuf = reinterpret_cast<float *>(fr_fb_smem);          // [FR_FB_QB][D]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t total = min((int64_t)(*n_rows), (int64_t)fb_max);
+    const int f0 = blockIdx.y * FR_FB_QB;
+    if (f0 >= total) return;
+    const int nf = (int)min((int64_t)FR_FB_QB, total - f0);
+    float qn[FR_FB_QB];
+    for (int u = 0; u < nf; ++u) {
+        const int64_t q = q0 + rows[f0 + u];
+        qn[u] = norms[q];
+        for (int j = threadIdx.x; j < D; j += blockDim.x) qbuf[u * D + j] = En[q * D + j];
+    }
+    __syncthreads();
+    for (int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp; c < n_db; c += (int64_t)gridDim.x * (blockDim.x >> 5)) {
+        const float *y = En + c * D;
+        float acc[FR_FB_QB];
+#pragma unroll
+        for (int u = 0; u < FR_FB_QB; ++u) acc[u] = 0.0f;
+        for (int j = lane; j < D; j += 32) {
+            const float yv = __ldg(&y[j]);
+#pragma unroll
+            for (int u = 0; u < FR_FB_QB; ++u)
+                if (u < nf) acc[u] = fmaf(qbuf[u * D + j], yv, acc[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < FR_FB_QB; ++u)
+            for (int s = 16; s > 0; s >>= 1) acc[u] += __shfl_xor_sync(0xFFFFFFFFu, acc[u], s);
+        const float cn = norms[c];
+        if (lane == 0) {
+#pragma unroll
+            for (int u = 0; u < FR_FB_QB; ++u)
+                if (u < nf) {
+                    const float d = (qn[u] == 0.0f || cn == 0.0f) ? 1.0f : 1.0f - acc[u];
+                    keys[(int64_t)(f0 + u) * n_db + c] = ((unsigned long long)fr_f2ord(d) << 32) | (unsigned long long)c;
+                }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+fr_knn_fb_select_kernel(const unsigned long long *__restrict__ keys, int64_t n_db, int k,
+                        const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int fb_max,
+                        int32_t *__restrict__ out_idx, float *__restrict__ out_dist) {
+    __shared__ int s_part[32];
+    __shared__ int s_total;
+    __shared__ int s_n;
+    __shared__ unsigned long long s_keys[FR_MAX_K * 2];
+    const int f = blockIdx.x;
+    if (f >= (int)min((int64_t)(*n_rows), (int64_t)fb_max)) return;
+    const unsigned long long *kp = keys + (int64_t)f * n_db;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // X = k-th smallest key: the largest x with count(keys < x) <= k - 1
+    unsigned long long X = 0;
+    for (int b = 63; b >= 0; --b) {
+        const unsigned long long cand = X | (1ull << b);
+        int c = 0;
+        for (int64_t i = threadIdx.x; i < n_db; i += blockDim.x) c += __ldcg(kp + i) < cand;
+        c = __reduce_add_sync(0xFFFFFFFFu, c);
+        if (lane == 0) s_part[warp] = c;
+        __syncthreads();
+        if (warp == 0) {
+            int t = lane < (int)(blockDim.x >> 5) ? s_part[lane] : 0;
+            t = __reduce_add_sync(0xFFFFFFFFu, t);
+            if (lane == 0) s_total = t;
+        }
+        __syncthreads();
+        if (s_total <= k - 1) X = cand;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) s_n = 0;
+    for (int i = threadIdx.x; i < FR_MAX_K * 2; i += blockDim.x) s_keys[i] = 0xFFFFFFFFFFFFFFFFull;
+    __syncthreads();
+    for (int64_t i = threadIdx.x; i < n_db; i += blockDim.x) {
+        const unsigned long long key = __ldcg(kp + i);
+        if (key <= X) { const int p = atomicAdd(&s_n, 1); if (p < FR_MAX_K * 2) s_keys[p] = key; }
+    }
+    __syncthreads();
+    // bitonic sort of 256 keys (keys are distinct: exactly k of them are real)
+    for (int kk = 2; kk <= FR_MAX_K * 2; kk <<= 1)
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+            const int i = threadIdx.x;
+            if (i < FR_MAX_K * 2) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const unsigned long long x = s_keys[i], y = s_keys[ixj];
+                    const bool up = (i & kk) == 0;
+                    if ((x > y) == up) { s_keys[i] = y; s_keys[ixj] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    const int64_t q = rows[f];
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        const unsigned long long key = s_keys[j];
+        out_idx[q * k + j] = (int32_t)(uint32_t)key;
+        out_dist[q * k + j] = fr_ord2f((uint32_t)(key >> 32));
+    }
+}
+
+int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
+                           int k, const int32_t *d_rows, const unsigned long long *d_n_rows, int32_t *d_idx,
+                           float *d_dist, int *rows_covered, cudaStream_t st) {
+    *rows_covered = 0;
+    if (k < 1 || k > FR_MAX_K || n_db < k) return FR_OK;
+    // scratch: fb_max x n_db keys, at most 256 MB
+    int fb_max = FR_FB_MAX;
+    while (fb_max > 1 && (int64_t)fb_max * n_db * 8 > (256ll << 20)) fb_max >>= 1;
+    if ((int64_t)fb_max * n_db * 8 > (1ll << 31)) return FR_OK;
+    int rc = fr_ensure(ctx, &ctx->d_knn_fb, &ctx->knn_fb_cap, (int64_t)fb_max * n_db * 8, "kNN fallback keys");
+    if (rc) return rc;
+    const size_t smem = (size_t)FR_FB_QB * D * sizeof(float);
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_fb_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)(ctx->sm_count * 4), (unsigned)((fb_max + FR_FB_QB - 1) / FR_FB_QB));
+    fr_kt_begin(ctx, "fr_knn_fb_dist_kernel", st);
+    fr_knn_fb_dist_kernel<<<grid, 256, smem, st>>>(d_En, d_norms, n_db, D, q0, d_rows, d_n_rows, fb_max,
+                                                   (unsigned long long *)ctx->d_knn_fb);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_fb_dist_kernel");
+    fr_kt_begin(ctx, "fr_knn_fb_select_kernel", st);
+    fr_knn_fb_select_kernel<<<fb_max, 1024, 0, st>>>((const unsigned long long *)ctx->d_knn_fb, n_db, k, d_rows,
+                                                     d_n_rows, fb_max, d_idx, d_dist);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_fb_select_kernel");
+    *rows_covered = fb_max;
     return FR_OK;
 }

@@ -28,7 +28,10 @@
 
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
-                        int32_t *d_idx, float *d_dist, cudaStream_t st);
+                        int64_t row_skip, int32_t *d_idx, float *d_dist, cudaStream_t st);
+int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
+                           int k, const int32_t *d_rows, const unsigned long long *d_n_rows, int32_t *d_idx,
+                           float *d_dist, int *rows_covered, cudaStream_t st);
 
 namespace {
 
@@ -695,7 +698,7 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
                      int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
     // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
     if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N)
-        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, d_idx, d_dist, st);
+        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     EncodeTiledFn encode = get_encode_fn();
     if (!encode) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled is not available");
     // selection window (how many candidates a compaction keeps) and the physical buffer size: a
@@ -724,8 +727,13 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
         if ((int)(b - a + 1) > p.slots) p.slots = (int)(b - a + 1);
     }
     if (p.slots > TC_MAX_SLOTS) return fr_fail(ctx, FR_ERR_STATE, "fr_knn: internal slot bound exceeded");
-    p.klo = 3 * win / 8;
-    p.khi = 5 * win / 8;
+    // a compaction keeps between klo and khi keys: enough beyond k that the k-th and the klo-th
+    // score are normally more than 2 eps apart (the K7 certificate), few enough that the running
+    // threshold stays tight (hits per row grow with the kept count)
+    p.klo = k + 30;
+    p.khi = p.klo + 48;
+    if (const char *e = getenv("FR_KNN_KLO")) p.klo = atoi(e);   // tuning experiments only
+    if (const char *e = getenv("FR_KNN_KHI")) p.khi = atoi(e);
     p.norms = d_norms;
 
     // workspace: keys | counts | thrs | fallback rows | fallback counter
@@ -779,7 +787,12 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
                 h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
     }
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
-    rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, d_idx, d_dist, st);
+    // ... the first few in parallel over the database (one warp per database row, then a block-wide
+    // exact selection per query), any beyond that by the one-warp-per-query scan
+    int covered = 0;
+    rc = fr_knn_fallback_launch(ctx, d_En, d_norms, n_db, D, q0, k, fb_rows, fb_count, d_idx, d_dist, &covered, st);
+    if (rc) return rc;
+    rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, covered, d_idx, d_dist, st);
     if (rc) return rc;
     FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[4], fb_count, 8, cudaMemcpyDeviceToHost, st));
     ctx->knn_fb_pending = true;

@@ -258,3 +258,22 @@ def test_host_path_chunked_equals_device_path(eng):
         assert torch.equal(a.embedding, b.embedding)
         assert torch.equal(a.nbr_idx, b.nbr_idx) and torch.equal(a.nbr_dist, b.nbr_dist)
         assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu()) and torch.equal(hb.nbr_dist, a.nbr_dist.cpu())
+
+
+def test_knn_uncertifiable_rows_take_exact_fallback(eng):
+    """Rows whose k-th neighbour is closer to the next ones than the fp16 bound cannot be
+    certified by the tensor-core pass; they are re-done exactly (in parallel over the database
+    for the first few, by the scan for the rest) and mode 0 still equals mode 1 bit for bit."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(3)
+    N, D, k = 6000, 96, 20
+    X = torch.randn((N, D), device="cuda", generator=g)
+    base = torch.randn((1, D), device="cuda", generator=g)
+    X[100:500] = base + 2e-4 * torch.randn((400, D), device="cuda", generator=g)     # 400 near-duplicates
+    En, Eh, norms = eng.normalize(X)
+    i0, d0 = eng.knn(En, Eh, norms, k, mode=0)
+    fb = eng.knn_fallback_rows
+    i1, d1 = eng.knn(En, Eh, norms, k, mode=1)
+    torch.cuda.synchronize()
+    assert fb > 40                       # more than one batch of the parallel fallback
+    assert torch.equal(d0, d1) and torch.equal(i0, i1)
