@@ -152,6 +152,7 @@ class Workload:
         R = self.plan.n_reads
         bounds = shard_reads(self.plan.pre_offsets, world)
         self.r0, self.r1 = int(bounds[rank]), int(bounds[rank + 1])
+        self.rows_per_rank = [2 * int(bounds[i + 1] - bounds[i]) for i in range(world)]   # known on every rank
         genome = SD.make_genome(w["genome"], w["seed"], device)
         self.bases, self.offsets = SD.generate_reads(self.plan, genome, self.r0, self.r1)
         del genome
@@ -290,7 +291,7 @@ def main():
 
     def device_step(timers=None):
         return run_hot_path(eng, wl.bases, offsets_d, P_dev, nk, k_nn, mode=args.knn_mode, group=group,
-                            timers=timers)
+                            timers=timers, rows_per_rank=wl.rows_per_rank)
 
     # ------------------------------------------------------------------ reference arm
     if args.impl == "reference":
@@ -355,9 +356,9 @@ def main():
     # ---- e2e: pinned host buffers -> public API -> pinned host results
     hb = HostBuffers.from_device(wl.bases, wl.offsets, 2 * wl.n_reads_local, min(k_nn, 2 * wl.n_reads_total))
     for _ in range(2):
-        run_hot_path_host(eng, hb, P_dev, nk, k_nn, mode=args.knn_mode, group=group)
+        run_hot_path_host(eng, hb, P_dev, nk, k_nn, mode=args.knn_mode, group=group, rows_per_rank=wl.rows_per_rank)
     sync_all()
-    e2e_steps = timed_steps(lambda: run_hot_path_host(eng, hb, P_dev, nk, k_nn, mode=args.knn_mode, group=group),
+    e2e_steps = timed_steps(lambda: run_hot_path_host(eng, hb, P_dev, nk, k_nn, mode=args.knn_mode, group=group, rows_per_rank=wl.rows_per_rank),
                             args.steps)
     sync_all()
     t = torch.tensor([float(sum(e2e_steps))], dtype=torch.float64, device=dev)

@@ -20,7 +20,7 @@ SYMBOLS = [
     "fr_profile_enable", "fr_profile_read",
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
     "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
-    "fr_knn", "fr_knn_last_fallback_rows",
+    "fr_knn", "fr_knn_rows_ready_after", "fr_knn_last_fallback_rows",
     "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
 ]
 
@@ -72,6 +72,7 @@ def lib():
     L.fr_project.argtypes = [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp]
     L.fr_normalize.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp, vp]
     L.fr_knn.argtypes = [vp, vp, vp, vp, i64, i32, i32, i64, i64, i32, i32, vp, vp, vp]
+    L.fr_knn_rows_ready_after.argtypes = [vp, vp]
     L.fr_knn_last_fallback_rows.argtypes = [vp]
     L.fr_knn_last_fallback_rows.restype = i64
     u64 = C.c_uint64

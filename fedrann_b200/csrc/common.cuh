@@ -81,6 +81,7 @@ struct fr_ctx {
     // K6/K7 scratch
     void *d_knn_ws = nullptr;
     int64_t knn_ws_cap = 0;
+    cudaEvent_t knn_en_event = nullptr;   // one-shot: the fp32 rows are complete once this event has fired
     void *d_knn_fb = nullptr;       // exact distances of the fallback rows (parallel fallback)
     int64_t knn_fb_cap = 0;
     int64_t knn_fallback_rows = 0;

@@ -29,6 +29,7 @@
 int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                         int64_t nq, int k, const int32_t *d_rows, const unsigned long long *d_n_rows,
                         int64_t row_skip, int32_t *d_idx, float *d_dist, cudaStream_t st);
+int fr_knn_wait_rows(fr_ctx *ctx, cudaStream_t st);
 int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                            int k, const int32_t *d_rows, const unsigned long long *d_n_rows, int32_t *d_idx,
                            float *d_dist, int *rows_covered, cudaStream_t st);
@@ -678,6 +679,10 @@ int tc_run(fr_ctx *ctx, const CUtensorMap &tmap, const TcParams &p, size_t smem,
     fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
     fr_knn_tc_kernel<CAP><<<p.n_ctas, TC_THREADS, smem, st>>>(tmap, p);
     FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
+    {   // K6 read only the fp16 copy; the fp32 rows (K7, fallback) may still be arriving (all-gather)
+        int rcw = fr_knn_wait_rows(ctx, st);
+        if (rcw) return rcw;
+    }
     int max_n = p.slots * CAP;                         // keys one row can hold across its buffers
     if (max_n > 4096) max_n = 4096;                    // (rows beyond it go to the exact scan)
     const size_t rsmem = (size_t)RR_WARPS * ((size_t)max_n * 8 + (size_t)RR_RES * 8);
@@ -697,6 +702,10 @@ int tc_run(fr_ctx *ctx, const CUtensorMap &tmap, const TcParams &p, size_t smem,
 int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
                      int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
     // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
+    if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N) {
+        int rcw = fr_knn_wait_rows(ctx, st);
+        if (rcw) return rcw;
+    }
     if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N)
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     EncodeTiledFn encode = get_encode_fn();

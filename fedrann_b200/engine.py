@@ -248,8 +248,13 @@ class Engine:
         return En, Eh, norms
 
     # -- K6 + K7 ---------------------------------------------------------
-    def knn(self, En, Eh, norms, k: int, q0: int = 0, nq: int | None = None, mode: int = 0):
+    def knn(self, En, Eh, norms, k: int, q0: int = 0, nq: int | None = None, mode: int = 0, rows_ready=None):
+        """rows_ready: a torch.cuda.Event after which En is complete (it may still be arriving from
+        an all-gather on another stream); the tensor-core pass does not wait for it."""
         N, D = En.shape
+        if rows_ready is not None:
+            check(self.h, self.L.fr_knn_rows_ready_after(self.h, C.c_void_p(rows_ready.cuda_event)),
+                  "fr_knn_rows_ready_after")
         nq = N - q0 if nq is None else nq
         idx = torch.empty((nq, k), dtype=torch.int32, device=En.device)
         dist = torch.empty((nq, k), dtype=torch.float32, device=En.device)

@@ -29,42 +29,79 @@ def init_from_env(backend: str | None = None):
 
 
 def shard_reads(offsets: np.ndarray, world: int) -> np.ndarray:
-    """Contiguous read ranges balanced by bases: returns int64[world+1] read
-    boundaries (rank r owns reads [b[r], b[r+1]))."""
-    offsets = np.asarray(offsets, dtype=np.int64)
-    R = len(offsets) - 1
-    total = int(offsets[-1] - offsets[0])
-    bounds = np.zeros(world + 1, dtype=np.int64)
-    for r in range(1, world):
-        target = offsets[0] + (total * r) // world
-        bounds[r] = int(np.searchsorted(offsets, target, side="left"))
-    bounds[world] = R
-    bounds = np.minimum(np.maximum.accumulate(bounds), R)
-    return bounds
+    """Contiguous read ranges with equal read COUNTS (+-1): returns int64[world+1] read
+    boundaries (rank r owns reads [b[r], b[r+1])).  Equal counts balance the dominant stage
+    exactly (every rank searches the same number of query rows) and let the embedding shards
+    be all-gathered in one collective without padding; bases per rank then differ by
+    O(1/sqrt(reads per rank)), which is what the extraction stage sees."""
+    R = len(np.asarray(offsets)) - 1
+    return np.array([(R * r) // world for r in range(world + 1)], dtype=np.int64)
 
 
-def all_gather_rows(En: torch.Tensor, Eh: torch.Tensor, norms: torch.Tensor, group=None):
+def all_gather_rows(En: torch.Tensor, Eh: torch.Tensor, norms: torch.Tensor, group=None, counts=None,
+                    overlap: bool = False):
     """All-gather row shards of unequal height.  Returns (En_all, Eh_all,
     norms_all, q0) where q0 is the global row number of this rank's first row
-    (rank-major order)."""
+    (rank-major order).  `counts` = rows per rank when the caller already knows
+    them (the read sharding is computed identically on every rank), which saves
+    the size exchange and its host synchronisation.  Every rank receives each
+    shard directly into its final place (no padding, no compaction copy).
+    With overlap=True a fifth value is returned, see below."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
-    n_local = torch.tensor([En.shape[0]], dtype=torch.int64, device=En.device)
-    counts = torch.zeros(world, dtype=torch.int64, device=En.device)
-    dist.all_gather_into_tensor(counts, n_local, group=group)
-    counts = [int(c) for c in counts.cpu()]
-    nmax = max(counts)
+    if counts is None:
+        n_local = torch.tensor([En.shape[0]], dtype=torch.int64, device=En.device)
+        cnt = torch.zeros(world, dtype=torch.int64, device=En.device)
+        dist.all_gather_into_tensor(cnt, n_local, group=group)
+        counts = [int(c) for c in cnt.cpu()]
+    counts = [int(c) for c in counts]
+    assert counts[rank] == En.shape[0]
+    total = sum(counts)
+    equal = all(c == counts[0] for c in counts)
 
     def gather(x):
-        pad = x
-        if x.shape[0] < nmax:
+        out = torch.empty((total,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        if equal:
+            dist.all_gather_into_tensor(out, x.contiguous(), group=group)
+        else:
+            # shards of different heights (reads not divisible by ranks): pad to the tallest, one
+            # collective, then copy into place
+            nmax = max(counts)
             pad = torch.zeros((nmax,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
             pad[: x.shape[0]] = x
-        out = torch.empty((world * nmax,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
-        dist.all_gather_into_tensor(out, pad.contiguous(), group=group)
-        if all(c == nmax for c in counts):
-            return out
-        return torch.cat([out[r * nmax: r * nmax + counts[r]] for r in range(world)], dim=0)
+            tmp = torch.empty((world * nmax,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+            if x.is_cuda:
+                dist.all_gather_into_tensor(tmp, pad, group=group)
+            else:
+                dist.all_gather(list(tmp.split(nmax, dim=0)), pad, group=group)   # gloo (CPU tests)
+            for r, dst in enumerate(out.split(counts, dim=0)):
+                dst.copy_(tmp[r * nmax: r * nmax + counts[r]])
+        return out
 
     q0 = sum(counts[:rank])
-    return gather(En), gather(Eh), gather(norms), q0
+    if not (overlap and En.is_cuda):
+        return gather(En), gather(Eh), gather(norms), q0
+    # The tensor-core pass needs only the fp16 copy and the norms: those are gathered first, on the
+    # caller's stream.  The fp32 rows (re-rank only) follow on a side stream; the returned event
+    # fires when they are complete (Engine.knn(rows_ready=...) waits for it just before the re-rank).
+    Eh_all, norms_all = gather(Eh), gather(norms)
+    cur = torch.cuda.current_stream()
+    side = _side_stream(En.device)
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        En_all = gather(En)
+        ev = torch.cuda.Event()
+        ev.record(side)
+    En.record_stream(side)
+    En_all.record_stream(cur)
+    return En_all, Eh_all, norms_all, q0, ev
+
+
+_side_streams: dict = {}
+
+
+def _side_stream(dev):
+    s = _side_streams.get(dev.index)
+    if s is None:
+        s = _side_streams[dev.index] = torch.cuda.Stream(device=dev)
+    return s

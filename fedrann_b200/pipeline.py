@@ -11,6 +11,12 @@ import torch
 from .engine import Engine
 
 
+# Gather the fp32 rows on a side stream while K6 runs (parallel.all_gather_rows(overlap=True)).
+# Off by default: measured on 4 x B200 the NCCL kernel and the persistent K6 CTAs compete for SMs
+# (K6 +8 %) and the step gets slower; at 2 ranks it gains 7 %.
+OVERLAP_ROW_GATHER = False
+
+
 @dataclass
 class StageTimes:
     """CUDA-event timers per stage (ms), accumulated over calls."""
@@ -50,7 +56,7 @@ class HotPathResult:
 
 def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev, nk: int, k_nn: int,
                  *, mode: int = 0, timers: StageTimes | None = None, docfreq: torch.Tensor | None = None,
-                 group=None) -> HotPathResult:
+                 group=None, rows_per_rank=None) -> HotPathResult:
     """bases/offsets: this rank's reads on the device.  With a process group the
     normalised embeddings of all ranks are all-gathered (NCCL) and this rank
     searches its own rows against the whole database; neighbour ids are global
@@ -65,15 +71,15 @@ def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev,
     t.start("normalize")
     En, Eh, norms = eng.normalize(E)
     t.stop()
-    q0, nq = 0, En.shape[0]
+    q0, nq, ready = 0, En.shape[0], []
     if group is not None and torch.distributed.get_world_size(group) > 1:
         t.start("allgather")
         from .parallel import all_gather_rows
-        En, Eh, norms, q0 = all_gather_rows(En, Eh, norms, group)
+        En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
         t.stop()
     t.start("knn")
     k_eff = min(k_nn, En.shape[0])
-    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode)
+    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None)
     t.stop()
     return HotPathResult(indptr, indices, E, idx, dist, q0)
 
@@ -106,7 +112,7 @@ class HostBuffers:
 
 
 def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *, mode: int = 0, group=None,
-                      timers: StageTimes | None = None, chunks: int = 8) -> HotPathResult:
+                      timers: StageTimes | None = None, chunks: int = 8, rows_per_rank=None) -> HotPathResult:
     """The call a host program makes: reads in pinned host memory -> device ->
     extract/project/kNN -> neighbour lists back in pinned host memory.  Returns
     after the results have landed.
@@ -156,12 +162,12 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
     indptr = torch.cat(ips) if ips else torch.zeros(1, dtype=torch.int64, device=dev)
     indices = torch.cat(ixs) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
     En, Eh, norms = eng.normalize(E)
-    q0, nq = 0, En.shape[0]
+    q0, nq, ready = 0, En.shape[0], []
     if group is not None and torch.distributed.get_world_size(group) > 1:
         from .parallel import all_gather_rows
-        En, Eh, norms, q0 = all_gather_rows(En, Eh, norms, group)
+        En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
     k_eff = min(k_nn, En.shape[0])
-    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode)
+    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None)
     res = HotPathResult(indptr, indices, E, idx, dist, q0)
     hb.nbr_idx[:, : res.nbr_idx.shape[1]].copy_(res.nbr_idx, non_blocking=True)
     hb.nbr_dist[:, : res.nbr_dist.shape[1]].copy_(res.nbr_dist, non_blocking=True)

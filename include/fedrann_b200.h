@@ -117,6 +117,11 @@ int fr_normalize(fr_ctx *ctx, const float *d_E, int64_t N, int D, int Dp, float 
 int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db,
            int D, int Dp, int64_t q0, int64_t nq, int k, int mode, int32_t *d_idx, float *d_dist,
            void *stream);
+/* Optional, before fr_knn: the fp32 rows d_En are still being written by other work (e.g. an
+ * all-gather on another stream) and are complete once `event` (a cudaEvent_t) has fired.  The
+ * tensor-core pass reads only the fp16 copy and starts at once; the first consumer of d_En
+ * waits for the event on fr_knn's stream.  One-shot: applies to the next fr_knn call only. */
+int fr_knn_rows_ready_after(fr_ctx *ctx, void *event);
 /* statistics of the last fr_knn call: rows that needed the exact fallback */
 int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
 

@@ -277,3 +277,25 @@ def test_knn_uncertifiable_rows_take_exact_fallback(eng):
     torch.cuda.synchronize()
     assert fb > 40                       # more than one batch of the parallel fallback
     assert torch.equal(d0, d1) and torch.equal(i0, i1)
+
+
+def test_knn_rows_ready_event(eng):
+    """fr_knn_rows_ready_after: the fp32 rows may still be arriving on another stream; the
+    tensor-core pass starts on the fp16 copy and only the re-rank waits for the event."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(9)
+    X = torch.randn((4000, 128), device="cuda", generator=g)
+    En, Eh, norms = eng.normalize(X)
+    i_ref, d_ref = eng.knn(En, Eh, norms, 15)
+    side = torch.cuda.Stream()
+    late = torch.zeros_like(En)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(20_000_000)            # ~10 ms: the rows land well after K6 has started
+        late.copy_(En)
+        ev = torch.cuda.Event()
+        ev.record(side)
+    i1, d1 = eng.knn(late, Eh, norms, 15, rows_ready=ev)
+    i2, d2 = eng.knn(late, Eh, norms, 15, mode=1)
+    torch.cuda.synchronize()
+    assert torch.equal(i1, i_ref) and torch.equal(d1, d_ref) and torch.equal(i2, i_ref)

@@ -38,11 +38,12 @@ def test_shard_reads_balanced_and_contiguous():
     rng = np.random.default_rng(0)
     lens = rng.integers(1, 20000, 1000)
     offs = np.concatenate([[0], np.cumsum(lens)])
-    for w in (1, 2, 4, 8):
+    for w in (1, 2, 3, 4, 8):
         b = shard_reads(offs, w)
         assert b[0] == 0 and b[-1] == 1000 and np.all(np.diff(b) >= 0)
+        assert np.diff(b).max() - np.diff(b).min() <= 1                  # equal read counts (+-1)
         sizes = [offs[b[r + 1]] - offs[b[r]] for r in range(w)]
-        assert max(sizes) - min(sizes) <= 2 * lens.max()
+        assert max(sizes) < 1.3 * (offs[-1] / w)                         # bases follow within noise
     assert list(shard_reads(np.array([0]), 4)) == [0, 0, 0, 0, 0]
 
 
