@@ -65,6 +65,7 @@ struct TcParams {
     int *counts;
     float *thrs;
     const float *norms;
+    unsigned int *gthr;        // [nq] per-row threshold shared by all CTAs working on the row (orderable float)
     unsigned long long *dbg;   // optional per-role wait-cycle counters (FR_KNN_DEBUG=1)
 };
 
@@ -406,7 +407,15 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             unsigned long long *buf = p.keys + stream * CAP;
             unsigned long long *ptr = sub ? buf + CAP - 1 : buf;     // this warp's end of the row's buffer
             int mycnt = 0;
-            if (sub == 0) s_thr[row_in_tile] = valid ? -INFINITY : INFINITY;
+            if (sub == 0) {
+                // start from whatever the row's other CTAs (or this CTA's earlier segment) reached
+                float t0v = INFINITY;
+                if (valid) {
+                    const unsigned int g = __ldcg(p.gthr + grow);
+                    t0v = g ? ord2f(g) : -INFINITY;
+                }
+                s_thr[row_in_tile] = t0v;
+            }
             tc_quad_bar(bar_id);
             for (int64_t t = t0; t < t1; ++t, ++tile) {
                 const uint32_t ab = tile & 1;
@@ -442,6 +451,14 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 // a buffer that could overflow during the next tile is compacted now
                 const int c0r = s_cnt[row_in_tile], c1r = s_cnt[TC_M + row_in_tile];
                 unsigned need = __ballot_sync(0xFFFFFFFFu, c0r + c1r > CAP - TC_N);
+                // A threshold reached by ANY CTA working on this query row is valid for all of them:
+                // that CTA keeps >= klo candidates at or above it.  Adopting it spares the CTAs that
+                // joined the row late (several slots per query tile: multi-GPU, small query sets)
+                // the slow climb from -inf.  s_thr only ever rises (it bounds everything dropped).
+                if (sub == 0 && valid) {
+                    const float gt = ord2f(__ldcg(p.gthr + grow));
+                    if (gt > s_thr[row_in_tile]) s_thr[row_in_tile] = gt;
+                }
                 tc_quad_bar(bar_id);                     // both warps hold the same counts before either rewrites them
                 if (need) {
                     unsigned mine = need;
@@ -455,7 +472,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                         const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n0, n1,
                                                                   p.klo, p.khi, &kept);
                         if (lane == src) {
-                            s_thr[row_in_tile] = nt;
+                            if (nt > s_thr[row_in_tile]) s_thr[row_in_tile] = nt;
+                            atomicMax(p.gthr + grow, f2ord(nt));
                             s_cnt[row_in_tile] = kept;
                             s_cnt[TC_M + row_in_tile] = 0;
                         }
@@ -748,7 +766,8 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     // workspace: keys | counts | thrs | fallback rows | fallback counter
     const int64_t streams = nq * p.slots;
     const size_t keys_b = (size_t)streams * cap * 8, cnt_b = ((size_t)streams * 4 + 15) & ~(size_t)15;
-    const size_t need = keys_b + 2 * cnt_b + (((size_t)nq * 4 + 15) & ~(size_t)15) + 16;
+    const size_t rows_b = ((size_t)nq * 4 + 15) & ~(size_t)15;
+    const size_t need = keys_b + 2 * cnt_b + 2 * rows_b + 16;
     int rc = fr_ensure(ctx, &ctx->d_knn_ws, &ctx->knn_ws_cap, (int64_t)need, "kNN workspace");
     if (rc) return rc;
     unsigned char *ws = (unsigned char *)ctx->d_knn_ws;
@@ -757,6 +776,8 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     p.thrs = (float *)(ws + keys_b + cnt_b);
     int32_t *fb_rows = (int32_t *)(ws + keys_b + 2 * cnt_b);
     unsigned long long *fb_count = (unsigned long long *)(ws + need - 16);
+    p.gthr = (unsigned int *)(ws + keys_b + 2 * cnt_b + rows_b);
+    FR_CUDA(ctx, cudaMemsetAsync(p.gthr, 0, rows_b, st));          // 0 orders below every float
     FR_CUDA(ctx, cudaMemsetAsync(p.counts, 0, cnt_b, st));
     FR_CUDA(ctx, cudaMemsetAsync(fb_count, 0, 16, st));
 
