@@ -254,9 +254,16 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 // lane quadrant fill the row's buffer from opposite ends, so no atomic is needed.
 __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
                                             unsigned long long *ptr, int step, int &pos, float thr) {
-    uint32_t mask = 0;
+    // four independent 4-bit chains (a single 16-deep funnel-shift chain is pure latency)
+    uint32_t m4[4];
 #pragma unroll
-    for (int j = 15; j >= 0; --j) mask = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[j])), mask, 1);
+    for (int g = 0; g < 4; ++g) {
+        m4[g] = 0;
+#pragma unroll
+        for (int j = 3; j >= 0; --j)
+            m4[g] = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[4 * g + j])), m4[g], 1);
+    }
+    uint32_t mask = (m4[0] | (m4[1] << 4)) | ((m4[2] << 8) | (m4[3] << 12));
     if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
         const int64_t left = n_db - (int64_t)cbase;
         mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
@@ -317,7 +324,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
 
     const int cta = blockIdx.x;
     const bool dbg_on = p.dbg != nullptr;
-    long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0, n_cmp = 0;
+    long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0, n_cmp = 0, n_hits = 0, n_hitmax = 0;
     const long long t_start = clock64();
     const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
     const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
@@ -425,24 +432,40 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
                 const int64_t col0 = t * TC_N;
                 const bool ragged = col0 + TC_N > p.n_db;
-                uint32_t va[TC_CH], vb[TC_CH];
-                tc_ld16(taddr + sub * TC_CH, va);
+                // TMEM loads run two chunks ahead of the filter: the warp's 8 chunks (alternate 16-column
+                // chunks of the tile) go through two 32-register buffers
+                const int cnt_at_tile_start = mycnt;
+                uint32_t a0[TC_CH], a1[TC_CH], b0[TC_CH], b1[TC_CH];
+                static_assert(TC_EPQ == 2 && TC_N / TC_CH == 16, "chunk schedule below assumes 2 warps x 8 chunks");
+                tc_ld16(taddr + sub * TC_CH, a0);
+                tc_ld16(taddr + (sub + 2) * TC_CH, a1);
 #pragma unroll 1
-                for (int c = sub; c < TC_N / TC_CH; c += 2 * TC_EPQ) {
+                for (int c = sub; c < TC_N / TC_CH; c += 8) {
                     long long tq = dbg_on ? clock64() : 0;
-                    tc_ld_wait();                                          // va landed
+                    tc_ld_wait();                                          // a0, a1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
-                    tc_ld16(taddr + (c + TC_EPQ) * TC_CH, vb);             // next own chunk in flight
-                    tc_filter16(va, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    tc_ld16(taddr + (c + 4) * TC_CH, b0);
+                    tc_ld16(taddr + (c + 6) * TC_CH, b1);
+                    tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
-                    tc_ld_wait();
+                    tc_ld_wait();                                          // b0, b1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
-                    if (c + 2 * TC_EPQ < TC_N / TC_CH) tc_ld16(taddr + (c + 2 * TC_EPQ) * TC_CH, va);
-                    tc_filter16(vb, (uint32_t)(col0 + (c + TC_EPQ) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    if (c + 8 < TC_N / TC_CH) {
+                        tc_ld16(taddr + (c + 8) * TC_CH, a0);
+                        tc_ld16(taddr + (c + 10) * TC_CH, a1);
+                    }
+                    tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
                 tc_fence_before();
+                if (dbg_on) {       // hits of this tile: total and the warp's largest per-lane count
+                    const int dh = mycnt - cnt_at_tile_start;
+                    n_hits += __reduce_add_sync(0xFFFFFFFFu, dh);
+                    n_hitmax += __reduce_max_sync(0xFFFFFFFFu, dh);
+                }
                 s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
@@ -505,6 +528,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             atomicAdd(&p.dbg[8], (unsigned long long)e_ld); atomicAdd(&p.dbg[9], (unsigned long long)e_flt);
             atomicAdd(&p.dbg[10], (unsigned long long)e_bar); atomicAdd(&p.dbg[11], (unsigned long long)e_cmp);
             atomicAdd(&p.dbg[12], (unsigned long long)n_cmp);
+            atomicAdd(&p.dbg[13], (unsigned long long)n_hits); atomicAdd(&p.dbg[14], (unsigned long long)n_hitmax);
         }
         if (warp == 0) atomicAdd(&p.dbg[5], (unsigned long long)life);
     }
@@ -815,6 +839,9 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
         const double ew = n * 4e6 * TC_EPQ;
         fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f (%.0f compactions per CTA)\n",
                 h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
+        fprintf(stderr, "[fr_knn dbg] hits per query row %.0f | per warp and tile: %.1f hits, largest per-lane count %.2f\n",
+                (double)h[13] / (double)p.nq, (double)h[13] / ((double)p.units * 4 * TC_EPQ),
+                (double)h[14] / ((double)p.units * 4 * TC_EPQ));
     }
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
     // ... the first few in parallel over the database (one warp per database row, then a block-wide
