@@ -1,6 +1,6 @@
 #!/bin/bash
 # K6 selection-window experiments on the c2 embeddings: time + fallback rows per (klo, khi)
-for CFG in "96 160" "80 128" "72 104" "64 96" "60 80" "112 192"; do
+for CFG in "80 128" "80 96" "80 88" "72 84" "66 76"; do
 set -- $CFG
 FR_KNN_KLO=$1 FR_KNN_KHI=$2 python - <<'PY'
 import os, sys, torch
