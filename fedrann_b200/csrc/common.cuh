@@ -29,7 +29,7 @@ struct FrTable {
     int k;
     int64_t n;     // number of features F
     // Set by fr_table_set_sampler once VERIFIED on the device: every key's canonical form c
-    // satisfies splitmix64(c ^ seed) < threshold (the library is a hash-threshold sample, as N1
+    // satisfies fr_sample_keep(c, seed, threshold) (the library is a hash-threshold sample, as N1
     // produces it).  K3 then rejects a position whose canonical k-mer fails that test in
     // registers, without touching the filter.
     int sampled;
@@ -121,6 +121,23 @@ __device__ __forceinline__ uint64_t fr_splitmix64(uint64_t x) {
     x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
     x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
     return x ^ (x >> 31);
+}
+// N1's sampler (DESIGN.md "N1"): a canonical k-mer c is sampled iff fr_sample_keep(c, seed, threshold),
+// threshold = fraction * 2^64.  A 32-bit mix (murmur3 finaliser over the folded k-mer) keeps the
+// test cheap enough to run once per read position in K3's register-only pre-filter.
+__host__ __device__ __forceinline__ uint32_t fr_sample_seedmix(uint64_t seed) {
+    return (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0x85EBCA77u);
+}
+__host__ __device__ __forceinline__ uint32_t fr_sample_hash(uint32_t lo, uint32_t hi, uint32_t seedmix) {
+    uint32_t x = lo ^ (hi * 0x9E3779B1u) ^ seedmix;
+    x ^= x >> 16; x *= 0x85EBCA6Bu;
+    x ^= x >> 13; x *= 0xC2B2AE35u;
+    x ^= x >> 16;
+    return x;
+}
+__host__ __device__ __forceinline__ bool fr_sample_keep(uint64_t c, uint64_t seed, uint64_t threshold) {
+    return threshold == 0xFFFFFFFFFFFFFFFFull ||
+           fr_sample_hash((uint32_t)c, (uint32_t)(c >> 32), fr_sample_seedmix(seed)) < (uint32_t)(threshold >> 32);
 }
 // Filter hash: 32-bit multiplicative.  k-mers of k <= 16 fit one word (hi == 0).
 #define FR_BLOOM_MUL1 0x9E3779B1u

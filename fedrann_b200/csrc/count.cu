@@ -4,7 +4,7 @@
 // reference samples k-mers AFTER counting with awk's rand(); that stream cannot be
 // reproduced without that awk binary and no test pins it, so
 // sampling here is a deterministic function of the canonical k-mer:
-//     keep(c) <=> splitmix64(c ^ seed) < fraction * 2^64
+//     keep(c) <=> fr_sample_keep(c, seed, fraction * 2^64)   (32-bit mix of the k-mer, common.cuh)
 // which commutes with counting -- only sampled k-mers ever enter the count table.
 // jellyfish semantics kept: canonical form = min(k-mer, reverse complement) on 2-bit
 // codes A0 C1 G2 T3, case-insensitive, windows containing a non-ACGT base or crossing a
@@ -13,13 +13,6 @@
 
 #define FC_THREADS 256
 #define FC_PPT 32
-
-__device__ __forceinline__ uint64_t fc_splitmix64(uint64_t x) {
-    x += 0x9E3779B97F4A7C15ull;
-    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
-    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
-    return x ^ (x >> 31);
-}
 
 __device__ __forceinline__ int fc_code(uint8_t b) {
     const uint8_t x = b & 0xDF;
@@ -52,7 +45,7 @@ fr_kmer_count_kernel(const uint8_t *__restrict__ bases, const int64_t *__restric
                 rc = (rc >> 2) | ((uint64_t)(3 - c) << rcsh);
                 if (++run < K || p < c0) continue;
                 const uint64_t can = fw < rc ? fw : rc;
-                if (fc_splitmix64(can ^ seed) >= threshold) continue;
+                if (!fr_sample_keep(can, seed, threshold)) continue;
                 uint32_t slot = fr_table_slot(fr_hash(can), lg_cap);
                 int tries = 0;
                 while (true) {

@@ -447,6 +447,7 @@ __device__ __forceinline__ uint32_t fr_filter32_sampled(uint32_t c0, uint32_t c1
                                                         uint32_t kmask_lo, uint32_t kmask_hi, uint64_t seed,
                                                         uint64_t threshold) {
     uint32_t pass = 0;
+    const uint32_t seedmix = fr_sample_seedmix(seed), thr32 = (uint32_t)(threshold >> 32);
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
         const int s = 62 - 2 * j;
@@ -465,17 +466,19 @@ __device__ __forceinline__ uint32_t fr_filter32_sampled(uint32_t c0, uint32_t c1
             rlo = __funnelshift_r(q0, q1, 2 * j);
             if (WIDE) rhi = __funnelshift_r(q1, q2, 2 * j);
         }
-        uint64_t fw, rc;
+        uint32_t keep;
         if (WIDE) {
-            fw = ((uint64_t)(hi & kmask_hi) << 32) | lo;
-            rc = ((uint64_t)(rhi & kmask_hi) << 32) | rlo;
+            const uint64_t fw = ((uint64_t)(hi & kmask_hi) << 32) | lo;
+            const uint64_t rc = ((uint64_t)(rhi & kmask_hi) << 32) | rlo;
+            const uint64_t can = fw < rc ? fw : rc;
+            keep = fr_sample_hash((uint32_t)can, (uint32_t)(can >> 32), seedmix) < thr32 ? 1u : 0u;
         } else {
-            fw = lo & kmask_lo;
-            rc = rlo & kmask_lo;
+            const uint32_t can = min(lo & kmask_lo, rlo & kmask_lo);
+            keep = fr_sample_hash(can, 0u, seedmix) < thr32 ? 1u : 0u;
         }
-        const uint64_t can = fw < rc ? fw : rc;
-        pass = (pass << 1) | (fr_splitmix64(can ^ seed) < threshold ? 1u : 0u);
+        pass = (pass << 1) | keep;
     }
+    if (threshold == 0xFFFFFFFFFFFFFFFFull) pass = 0xFFFFFFFFu;     // fraction 1: everything is sampled
     return pass;
 }
 

@@ -67,7 +67,7 @@ __global__ void fr_table_verify_sampler_kernel(const uint4 *__restrict__ slots, 
         uint64_t rc = 0, x = key;
         for (int j = 0; j < K; ++j) { rc = (rc << 2) | (3ull - (x & 3ull)); x >>= 2; }
         const uint64_t can = key < rc ? key : rc;
-        if (fr_splitmix64(can ^ seed) >= threshold) atomicAdd(bad, 1ull);
+        if (!fr_sample_keep(can, seed, threshold)) atomicAdd(bad, 1ull);
     }
 }
 

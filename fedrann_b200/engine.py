@@ -185,7 +185,7 @@ class Engine:
     def build_table(self, codes, k: int, sampler=None) -> None:
         """codes: uint64 numpy (or int64-viewed cuda tensor), feature index -> k-mer code.
         sampler = (seed, fraction) declares that the library was sampled by N1's rule
-        (splitmix64(canonical ^ seed) < fraction * 2^64); the claim is verified on the device and
+        (fr_sample_keep(canonical, seed, fraction * 2^64), csrc/common.cuh); the claim is verified on the device and
         `self.sampled` tells whether extraction will use it."""
         if isinstance(codes, np.ndarray):
             codes = self.dev(np.ascontiguousarray(codes, dtype=np.uint64).view(np.int64))

@@ -27,6 +27,26 @@ def splitmix64(x: np.ndarray) -> np.ndarray:
     return x
 
 
+def sample_keep(codes: np.ndarray, seed: int, fraction: float) -> np.ndarray:
+    """N1's sampler (csrc/common.cuh fr_sample_keep): a canonical k-mer c is sampled iff
+    fmix32(lo(c) ^ hi(c)*0x9E3779B1 ^ seedmix) < floor(fraction * 2^64) >> 32 (everything at fraction 1)."""
+    m32 = np.uint64(0xFFFFFFFF)
+    thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
+    c = codes.astype(np.uint64)
+    if thr == 2 ** 64 - 1:
+        return np.ones(len(c), dtype=bool)
+    seed &= 2 ** 64 - 1
+    seedmix = (seed & 0xFFFFFFFF) ^ (((seed >> 32) * 0x85EBCA77) & 0xFFFFFFFF)
+    with np.errstate(over="ignore"):
+        x = (c & m32) ^ (((c >> np.uint64(32)) * np.uint64(0x9E3779B1)) & m32) ^ np.uint64(seedmix)
+        x ^= x >> np.uint64(16)
+        x = (x * np.uint64(0x85EBCA6B)) & m32
+        x ^= x >> np.uint64(13)
+        x = (x * np.uint64(0xC2B2AE35)) & m32
+        x ^= x >> np.uint64(16)
+    return x < np.uint64(thr >> 32)
+
+
 def kmer_codes(codes2: np.ndarray, k: int) -> np.ndarray:
     """All k-mer codes (A0 C1 G2 T3, first base most significant, the encoding
     of kmer_searcher.cpp:138-151) of a 0..3 coded sequence."""
@@ -170,7 +190,7 @@ def simulate_reads(genome: np.ndarray, coverage: float, seed: int, *, mean_len: 
 def library_from_reads(reads: ReadSet, k: int, fraction: float, min_mult: int, seed: int) -> KmerLibrary:
     """Exact harness-side stand-in for `jellyfish count -C` + `dump -L` + the awk
     sampler (count_kmers.py:80-123): canonical k-mers of all reads with
-    multiplicity >= min_mult, kept when splitmix64(code ^ seed) < fraction*2^64.
+    multiplicity >= min_mult, kept when sample_keep(code, seed, fraction).
     Windows containing a non-ACGT base are skipped (jellyfish does the same).
     Small inputs only (np.unique over every k-mer)."""
     lut = np.full(256, 4, dtype=np.uint8)
@@ -204,9 +224,7 @@ def library_from_genome(genome: np.ndarray, k: int, fraction: float, coverage: f
 
 
 def _sample(codes, counts, k, fraction, seed) -> KmerLibrary:
-    h = splitmix64(codes ^ np.uint64(seed))
-    thr = np.uint64(min(int(fraction * 2.0 ** 64), 2 ** 64 - 1))
-    keep = h < thr
+    keep = sample_keep(codes, seed, fraction)
     codes, counts = codes[keep], counts[keep]
     # jellyfish dumps in hash order, not sorted order: shuffle deterministically
     order = np.argsort(splitmix64(codes + np.uint64(seed)), kind="stable")

@@ -216,6 +216,23 @@ def revcomp_codes_t(x: torch.Tensor, k: int) -> torch.Tensor:
     return _lsr(x, 64 - 2 * k) if k < 32 else x
 
 
+def sample_keep_t(c: torch.Tensor, seed: int, fraction: float) -> torch.Tensor:
+    """synthetic.sample_keep on int64 lanes (the low 32 bits of an int64 product are exact)."""
+    thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
+    if thr == 2 ** 64 - 1:
+        return torch.ones_like(c, dtype=torch.bool)
+    seed &= 2 ** 64 - 1
+    seedmix = (seed & 0xFFFFFFFF) ^ (((seed >> 32) * 0x85EBCA77) & 0xFFFFFFFF)
+    m32 = 0xFFFFFFFF
+    x = (c & m32) ^ ((_lsr(c, 32) * 0x9E3779B1) & m32) ^ seedmix
+    x = x ^ (x >> 16)
+    x = (x * 0x85EBCA6B) & m32
+    x = x ^ (x >> 13)
+    x = (x * 0xC2B2AE35) & m32
+    x = x ^ (x >> 16)
+    return x < (thr >> 32)
+
+
 def sampled_kmer_counts(bases: torch.Tensor, offsets: np.ndarray, k: int, fraction: float, seed: int,
                         *, chunk_bases: int = 1 << 25):
     """(codes int64 sorted, counts int64) of the canonical k-mers of these reads
@@ -245,7 +262,7 @@ def sampled_kmer_counts(bases: torch.Tensor, offsets: np.ndarray, k: int, fracti
         ok &= (pos + k) <= offs_d[rid + 1]
         km = kmer_codes_t(c & 3, k)[ok]
         can = torch.minimum(km, revcomp_codes_t(km, k))
-        keep = _u64_less(splitmix64_t(can ^ _i64(seed)), thr)
+        keep = sample_keep_t(can, seed, fraction)
         acc.append(can[keep])
         del c, bad, cb, ok, pos, rid, km, can, keep
     allc = torch.cat(acc) if acc else torch.zeros(0, dtype=torch.int64, device=dev)

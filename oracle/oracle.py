@@ -323,7 +323,8 @@ def count_kmers(bases: np.ndarray, offsets: np.ndarray, k: int, fraction: float,
     (fedrann/count_kmers.py:76-123): canonical k-mers (min of k-mer and reverse complement,
     A0 C1 G2 T3) of every read, windows with a non-ACGT base skipped, multiplicity >= min_mult.
     The reference's awk rand() sampler is unpinned; the build's sampler is
-    keep(c) <=> splitmix64(c ^ seed) < fraction * 2^64.  -> {code: count} (plain Python loop:
+    keep(c) <=> fmix32(lo(c) ^ hi(c)*0x9E3779B1 ^ seedmix(seed)) < (fraction * 2^64) >> 32, everything at
+    fraction 1 (csrc/common.cuh fr_sample_keep).  -> {code: count} (plain Python loop:
     small inputs only)."""
     code = {65: 0, 67: 1, 71: 2, 84: 3, 97: 0, 99: 1, 103: 2, 116: 3}
     mask = (1 << (2 * k)) - 1
@@ -342,10 +343,22 @@ def count_kmers(bases: np.ndarray, offsets: np.ndarray, k: int, fraction: float,
             if run >= k:
                 can = min(fw, rc)
                 counts[can] = counts.get(can, 0) + 1
-    keys = np.array(sorted(counts), dtype=np.uint64)
     thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
-    h = _splitmix64(keys ^ np.uint64(seed & (2 ** 64 - 1)))
-    return {int(c): counts[int(c)] for c, hh in zip(keys, h) if int(hh) < thr and counts[int(c)] >= min_mult}
+    sd = seed & (2 ** 64 - 1)
+    seedmix = (sd & 0xFFFFFFFF) ^ (((sd >> 32) * 0x85EBCA77) & 0xFFFFFFFF)
+
+    def keep(c):        # fr_sample_keep (csrc/common.cuh), plain integers
+        if thr == 2 ** 64 - 1:
+            return True
+        x = (c & 0xFFFFFFFF) ^ (((c >> 32) * 0x9E3779B1) & 0xFFFFFFFF) ^ seedmix
+        x ^= x >> 16
+        x = (x * 0x85EBCA6B) & 0xFFFFFFFF
+        x ^= x >> 13
+        x = (x * 0xC2B2AE35) & 0xFFFFFFFF
+        x ^= x >> 16
+        return x < (thr >> 32)
+
+    return {c: n for c, n in counts.items() if n >= min_mult and keep(c)}
 
 
 def overlaps_tsv(neighbor_matrix: np.ndarray, neighbor_distances: np.ndarray, read_names, strands) -> str:

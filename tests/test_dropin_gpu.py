@@ -156,3 +156,46 @@ def test_reference_named_functions(tmp_path):
     assert np.allclose(dist, od, atol=1e-5) and (idx == oi).mean() > 0.99
     with pytest.raises(ValueError):
         NNDescent_ava().get_neighbors(E, metric="euclidean")
+
+
+def _run_cli(tmp_path, fasta_bytes, name="r.fa", extra=()):
+    fa = tmp_path / name
+    fa.write_bytes(fasta_bytes)
+    out = tmp_path / "out"
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "-m", "fedrann_b200", "-i", str(fa), "-o", str(out), "-k", "11",
+                        "--kmer-sample-fraction", "0.5", "-n", "32", "--nndescent-n-neighbors", "5", *extra],
+                       capture_output=True, text=True, env=env)
+    return r, out
+
+
+def test_cli_edge_inputs(tmp_path):
+    """Ragged and degenerate inputs through the whole CLI: reads shorter than k, N runs, a read
+    without any library k-mer, fewer rows than neighbours asked for."""
+    rng = np.random.default_rng(0)
+    core = "".join("ACGT"[i] for i in rng.integers(0, 4, 400))
+    recs = [("a", core[:300]), ("b", core[50:350]), ("short", "ACG"), ("ns", "N" * 40), ("c", core[100:400]),
+            ("lower", core[:200].lower()), ("poly", "A" * 100)]
+    fasta = "".join(f">{n} desc\n{s}\n" for n, s in recs).encode()
+    r, out = _run_cli(tmp_path, fasta)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = (out / "overlaps.tsv").read_text().splitlines()
+    assert lines[0].split("\t") == ["query_name", "query_orientation", "target_name", "target_orientation",
+                                    "neighbor_rank", "distance"]
+    assert not (out / "temp").exists()                                  # removed without --keep-intermediates
+    body = [ln.split("\t") for ln in lines[1:]]
+    assert 14 * 4 <= len(body) <= 14 * 5                                # self filtered where it is listed
+    # overlapping reads find each other first
+    first = {(q, qo): t for q, qo, t, to, rk, d in body if rk == "1"}
+    assert first[("a", "+")] in ("b", "lower", "c") and first[("b", "+")] in ("a", "c", "lower")
+    # a single read: k is clamped to the row count
+    (tmp_path / "one").mkdir()
+    r, out = _run_cli(tmp_path / "one", b">x\n" + core.encode() + b"\n", extra=("--kmer-min-multiplicity", "1"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    rows = (out / "overlaps.tsv").read_text().splitlines()[1:]
+    assert len(rows) == 2 and {ln.split("\t")[2] for ln in rows} == {"x"}
+
+
+def test_cli_rejects_unknown_format(tmp_path):
+    r, _ = _run_cli(tmp_path, b">x\nACGT\n", name="reads.txt")
+    assert r.returncode != 0 and "Unsupported file format" in r.stderr
