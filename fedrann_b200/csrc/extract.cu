@@ -3,7 +3,9 @@
 // :333-341, probe :325-326 / :343-344, per-read dedupe :327 / :345) and the
 // result collection of :90-96.
 //
-// One CTA per read.  The read is walked in tiles of FR_TILE positions:
+// One CTA (128 threads, 8 resident per SM: the phases of a read -- pack, filter, probe, sort --
+// are separated by block barriers, and it is the number of reads in flight per SM that hides
+// their latencies) per read.  The read is walked in tiles of FR_TILE = 4096 positions:
 //   K1  the tile's ASCII is loaded with 16-byte vector loads and packed to
 //       2-bit codes (first base in the most significant bits, so that a k-mer
 //       is a funnel shift of two packed words) + a 1-bit "non-ACGT" mask;
@@ -27,13 +29,13 @@
 
 #include <cstdlib>
 
-#define FR_THREADS 256
+#define FR_THREADS 128
 #define FR_PPT 32                       // positions per thread per tile
-#define FR_TILE (FR_THREADS * FR_PPT)   // 8192 positions
-#define FR_QCAP 2048                    // deferred k-mer queue; drained when a tile might not fit
-#define FR_HCAP 4096                    // shared-memory hit list
+#define FR_TILE (FR_THREADS * FR_PPT)   // 4096 positions
+#define FR_QCAP 1024                    // deferred k-mer queue; drained when a tile might not fit
+#define FR_HCAP 2048                    // shared-memory hit list
 #define FR_NWORDS (FR_TILE / 16 + 2)    // packed words incl. 32 positions of look-behind
-#define FR_MAXB 64                      // most sort buckets (FR_HCAP / 64)
+#define FR_MAXB 32                      // most sort buckets (FR_HCAP / 64)
 #define FR_BCAP 128                     // entries one warp sorts in registers
 
 #define FR_FLAG_SCRATCH_OVERFLOW 1ull
@@ -483,7 +485,7 @@ __device__ __forceinline__ uint32_t fr_filter32_sampled(uint32_t c0, uint32_t c1
 }
 
 template <bool WIDE, bool SAMPLED>
-__global__ void __launch_bounds__(FR_THREADS, 4)
+__global__ void __launch_bounds__(FR_THREADS, 8)
 fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int64_t *__restrict__ offsets,
                   int64_t n_reads, FrTable tb, int32_t *scratch, int64_t scratch_cap, uint32_t *spill,
                   int64_t spill_cap, int64_t *read_off, int32_t *read_cnt, unsigned long long *counters, int dbg) {
@@ -685,7 +687,7 @@ __global__ void fr_docfreq_kernel(const int32_t *__restrict__ scratch, int64_t n
 int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,
                       int64_t n_reads, uint32_t *d_docfreq, cudaStream_t st) {
     (void)d_docfreq;
-    int64_t grid = n_reads < (int64_t)ctx->sm_count * 64 ? n_reads : (int64_t)ctx->sm_count * 64;
+    int64_t grid = n_reads < (int64_t)ctx->sm_count * 128 ? n_reads : (int64_t)ctx->sm_count * 128;
     if (grid < 1) grid = 1;
     typedef void (*KernelFn)(const uint8_t *, int64_t, const int64_t *, int64_t, FrTable, int32_t *, int64_t, uint32_t *,
                              int64_t, int64_t *, int32_t *, unsigned long long *, int);

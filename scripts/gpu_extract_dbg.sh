@@ -1,7 +1,7 @@
 #!/bin/bash
 # timing experiments on the extract kernel: FR_EXTRACT_DEBUG bits (1 no table probes, 2 no filter loads, 4 no sort, 8 generic filter)
 mkdir -p gpurun_out
-for CFG in 0 1; do for FL in 1 0; do export FR_FLUSH=$FL
+for CFG in 0 1 4; do for FL in 1; do export FR_FLUSH=$FL
 FR_EXTRACT_DEBUG=$CFG python - <<'PY'
 import os, torch, numpy as np, sys
 sys.path.insert(0, '.')
