@@ -76,7 +76,9 @@ int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, int k, void 
 
 /* Optional, after fr_table_build: declare that the library is a hash-threshold sample -- every
  * key's canonical k-mer c (min of the k-mer and its reverse complement) satisfies
- * fr_sample_keep(c, seed, threshold) (a 32-bit murmur-style mix of the k-mer and the seed against the top 32 bits of threshold; everything passes at threshold = 2^64 - 1), which is how N1 (fr_kmer_count_*) samples.  The claim is
+ * the sampling rule of csrc/common.cuh (`fr_sample_keep`: a 32-bit murmur-style mix of the
+ * k-mer and the seed, compared with the top 32 bits of threshold; everything passes at
+ * threshold = 2^64 - 1), which is how N1 (fr_kmer_count_*) samples.  The claim is
  * VERIFIED on the device for every key; FR_ERR_ARG (and no change of behaviour) when it does not
  * hold.  When it holds, extraction rejects positions whose canonical k-mer fails the same test
  * in registers; results are identical either way. */
@@ -129,8 +131,9 @@ int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
  * Replaces the pre-step of run_kmer_searcher (fedrann/count_kmers.py:76-123:
  * `jellyfish count -C`, `jellyfish dump -L <min-mult>`, the awk sampler).
  * A canonical k-mer c (min of the k-mer and its reverse complement, codes A0 C1
- * G2 T3) is sampled iff fr_sample_keep(c, seed, threshold) (a 32-bit murmur-style mix of the k-mer and the seed against the top 32 bits of threshold; everything passes at threshold = 2^64 - 1) (threshold =
- * fraction * 2^64); windows with a non-ACGT base or crossing a read boundary
+ * G2 T3) is sampled iff it passes `fr_sample_keep` (csrc/common.cuh: a 32-bit
+ * murmur-style mix of the k-mer and the seed, compared with the top 32 bits of
+ * threshold = fraction * 2^64; everything passes at 2^64 - 1); windows with a non-ACGT base or crossing a read boundary
  * are skipped.  begin() sizes and clears the count table (capacity = slots, a
  * power of two is chosen >= capacity), add() may be called once per batch of
  * reads and returns the number of distinct sampled k-mers so far (FR_ERR_NOMEM
