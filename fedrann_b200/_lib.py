@@ -19,8 +19,9 @@ SYMBOLS = [
     "fr_version", "fr_create", "fr_destroy", "fr_last_error", "fr_launch_count",
     "fr_profile_enable", "fr_profile_read",
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
-    "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_project", "fr_normalize",
+    "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_extract_async", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_rows_ready_after", "fr_knn_last_fallback_rows",
+    "fr_knn_inc_begin", "fr_knn_inc_phase", "fr_knn_inc_finish",
     "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
 ]
 
@@ -69,10 +70,14 @@ def lib():
     L.fr_table_build.argtypes = [vp, vp, i64, i32, vp]
     L.fr_extract_count.argtypes = [vp, vp, i64, vp, i64, vp, vp, C.POINTER(i64), vp]
     L.fr_extract_fill.argtypes = [vp, vp, vp]
+    L.fr_extract_async.argtypes = [vp, vp, i64, vp, i64, vp, vp, i64, vp, vp]
     L.fr_project.argtypes = [vp, vp, vp, i64, vp, vp, vp, i64, i32, vp, vp]
     L.fr_normalize.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp, vp]
     L.fr_knn.argtypes = [vp, vp, vp, vp, i64, i32, i32, i64, i64, i32, i32, vp, vp, vp]
     L.fr_knn_rows_ready_after.argtypes = [vp, vp]
+    L.fr_knn_inc_begin.argtypes = [vp, vp, vp, vp, i64, i32, i32, i32, i32, vp, vp]
+    L.fr_knn_inc_phase.argtypes = [vp, i32, vp]
+    L.fr_knn_inc_finish.argtypes = [vp, vp, vp, vp]
     L.fr_knn_last_fallback_rows.argtypes = [vp]
     L.fr_knn_last_fallback_rows.restype = i64
     u64 = C.c_uint64

@@ -119,10 +119,11 @@ extern "C" void fr_destroy(fr_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->d_bloom); cudaFree(ctx->d_slots); cudaFree(ctx->d_cslots);
     cudaFree(ctx->d_scratch); cudaFree(ctx->d_spill); cudaFree(ctx->d_read_off);
-    cudaFree(ctx->d_read_cnt); cudaFree(ctx->d_counters); cudaFree(ctx->d_scan_tmp);
+    cudaFree(ctx->d_read_cnt); cudaFree(ctx->d_read_order); cudaFree(ctx->d_counters); cudaFree(ctx->d_scan_tmp);
     cudaFree(ctx->d_knn_ws); cudaFree(ctx->d_knn_fb); cudaFree(ctx->d_count_slots);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     fr_kt_clear(ctx);
+    if (ctx->knn_inc && ctx->knn_inc_free) ctx->knn_inc_free(ctx->knn_inc);
     delete ctx;
 }
 
@@ -145,10 +146,12 @@ extern "C" int fr_extract_count(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_b
     if (ctx->reads_cap < n_reads || !ctx->d_read_off) {
         if (ctx->d_read_off) cudaFree(ctx->d_read_off);
         if (ctx->d_read_cnt) cudaFree(ctx->d_read_cnt);
-        ctx->d_read_off = nullptr; ctx->d_read_cnt = nullptr;
+        if (ctx->d_read_order) cudaFree(ctx->d_read_order);
+        ctx->d_read_off = nullptr; ctx->d_read_cnt = nullptr; ctx->d_read_order = nullptr;
         int64_t cap = n_reads > 0 ? n_reads : 1;
         FR_CUDA(ctx, cudaMalloc(&ctx->d_read_off, (size_t)cap * 8));
         FR_CUDA(ctx, cudaMalloc(&ctx->d_read_cnt, (size_t)cap * 4));
+        FR_CUDA(ctx, cudaMalloc(&ctx->d_read_order, (size_t)cap * 4));
         ctx->reads_cap = cap;
     }
     // first guess: one hit per 8 bases (sample fractions <= 0.05 give <= 1/20)
@@ -199,6 +202,46 @@ extern "C" int fr_extract_count(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_b
         }
     }
     return fr_fail(ctx, FR_ERR_STATE, "fr_extract_count: scratch sizing did not converge");
+}
+
+extern "C" int fr_extract_async(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,
+                                int64_t n_reads, int64_t *d_indptr, int32_t *d_indices, int64_t cap,
+                                int64_t *d_status, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    if (!ctx->has_table) return fr_fail(ctx, FR_ERR_STATE, "fr_extract_async: no table (call fr_table_build)");
+    if (n_reads < 0 || n_bases < 0 || cap < 0 || !d_offsets || !d_indptr || !d_indices || !d_status)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_extract_async: bad argument");
+    if (((uintptr_t)d_bases & 15) != 0)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_extract_async: d_bases must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    ctx->last_n_reads = -1;
+    if (ctx->reads_cap < n_reads || !ctx->d_read_off) {       // (allocation = a device-wide sync, first call only)
+        if (ctx->d_read_off) cudaFree(ctx->d_read_off);
+        if (ctx->d_read_cnt) cudaFree(ctx->d_read_cnt);
+        if (ctx->d_read_order) cudaFree(ctx->d_read_order);
+        ctx->d_read_off = nullptr; ctx->d_read_cnt = nullptr; ctx->d_read_order = nullptr;
+        int64_t rcap = n_reads > 0 ? n_reads : 1;
+        FR_CUDA(ctx, cudaMalloc(&ctx->d_read_off, (size_t)rcap * 8));
+        FR_CUDA(ctx, cudaMalloc(&ctx->d_read_cnt, (size_t)rcap * 4));
+        FR_CUDA(ctx, cudaMalloc(&ctx->d_read_order, (size_t)rcap * 4));
+        ctx->reads_cap = rcap;
+    }
+    // scratch for as many hits as the caller has room for (at least the first guess of fr_extract_count)
+    int64_t want = n_bases / 8 + n_reads + 1024;
+    if (want < cap + n_reads) want = cap + n_reads;
+    if (ctx->scratch_cap < want) {
+        int64_t capb = ctx->scratch_cap * 4;
+        int rc = fr_ensure(ctx, (void **)&ctx->d_scratch, &capb, want * 4, "scratch");
+        if (rc) return rc;
+        ctx->scratch_cap = capb / 4;
+    }
+    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 8 * sizeof(unsigned long long), st));
+    int rc = fr_extract_launch(ctx, d_bases, n_bases, d_offsets, n_reads, nullptr, st);
+    if (rc) return rc;
+    rc = fr_scan_counts(ctx, ctx->d_read_cnt, n_reads, d_indptr, st);
+    if (rc) return rc;
+    return fr_gather_rows_checked(ctx, d_indptr, n_reads, d_indices, cap, (long long *)d_status, st);
 }
 
 extern "C" int fr_extract_fill(fr_ctx *ctx, int32_t *d_indices, void *stream) {

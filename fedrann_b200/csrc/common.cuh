@@ -56,6 +56,7 @@ struct fr_ctx {
     int64_t spill_cap = 0;
     int64_t *d_read_off = nullptr;  // [n_reads] offset into d_scratch
     int32_t *d_read_cnt = nullptr;  // [n_reads]
+    int32_t *d_read_order = nullptr; // [n_reads] reads longest first
     int64_t reads_cap = 0;
     unsigned long long *d_counters = nullptr;  // [0] scratch used, [1] spill used, [2] flags
     unsigned long long *h_counters = nullptr;  // pinned mirror
@@ -87,6 +88,8 @@ struct fr_ctx {
     int64_t knn_fallback_rows = 0;
     bool knn_fb_pending = false;    // h_counters[4] holds the count once knn_fb_stream has drained
     cudaStream_t knn_fb_stream = nullptr;
+    void *knn_inc = nullptr;        // state of an incremental search (fr_knn_inc_*), owned by knn_tc.cu
+    void (*knn_inc_free)(void *) = nullptr;
 };
 
 int fr_fail(fr_ctx *ctx, int code, const char *what);
@@ -155,4 +158,6 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
                       int64_t n_reads, uint32_t *d_docfreq, cudaStream_t st);
 int fr_scan_counts(fr_ctx *ctx, const int32_t *d_cnt, int64_t n, int64_t *d_indptr, cudaStream_t st);
 int fr_gather_rows(fr_ctx *ctx, int32_t *d_indices, cudaStream_t st);
+int fr_gather_rows_checked(fr_ctx *ctx, int64_t *d_indptr, int64_t n, int32_t *d_indices, int64_t cap,
+                           long long *d_status, cudaStream_t st);
 int fr_docfreq_launch(fr_ctx *ctx, int64_t nnz, uint32_t *d_docfreq, cudaStream_t st);

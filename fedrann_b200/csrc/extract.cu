@@ -488,7 +488,8 @@ template <bool WIDE, bool SAMPLED>
 __global__ void __launch_bounds__(FR_THREADS, 8)
 fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int64_t *__restrict__ offsets,
                   int64_t n_reads, FrTable tb, int32_t *scratch, int64_t scratch_cap, uint32_t *spill,
-                  int64_t spill_cap, int64_t *read_off, int32_t *read_cnt, unsigned long long *counters, int dbg) {
+                  int64_t spill_cap, int64_t *read_off, int32_t *read_cnt, unsigned long long *counters,
+                  const int32_t *__restrict__ order, int dbg) {
     extern __shared__ __align__(16) unsigned char fr_extract_smem[];
     FrExtractShared &sh = *reinterpret_cast<FrExtractShared *>(fr_extract_smem);
     const int tid = threadIdx.x, lane = tid & 31;
@@ -496,7 +497,8 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
     const uint64_t kmask = (1ull << (2 * K)) - 1;
     const uint32_t kmask_lo = (uint32_t)kmask, kmask_hi = (uint32_t)(kmask >> 32);
     const int wsh = 32 - tb.lg_words, bsh = 27 - tb.lg_words;
-    for (int64_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
+    for (int64_t ri = blockIdx.x; ri < n_reads; ri += gridDim.x) {
+        const int64_t r = order[ri];                       // longest reads first (fr_read_order_kernel)
         const int64_t s = offsets[r], e = offsets[r + 1];
         const int64_t len = e - s;
         const int64_t n_lookups = len >= K ? len - K + 1 : 1;
@@ -632,6 +634,33 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
     }
 }
 
+// ---- read order: one CTA per read means the longest read of a launch sets its tail.  Reads are
+// issued longest first (CTAs start in blockIdx order): a counting sort by length / 1024, done by
+// one CTA with shared-memory atomics (the order inside a bucket does not matter; rows still land
+// in input order).
+#define FR_LEN_BUCKETS 64
+__global__ void __launch_bounds__(1024) fr_read_order_kernel(const int64_t *__restrict__ offsets, int64_t n_reads,
+                                                            int32_t *__restrict__ order) {
+    __shared__ int s_cnt[FR_LEN_BUCKETS];
+    const int tid = threadIdx.x;
+    if (tid < FR_LEN_BUCKETS) s_cnt[tid] = 0;
+    __syncthreads();
+    for (int64_t r = tid; r < n_reads; r += blockDim.x) {
+        const int64_t b = (offsets[r + 1] - offsets[r]) >> 10;
+        atomicAdd(&s_cnt[b < FR_LEN_BUCKETS - 1 ? (int)b : FR_LEN_BUCKETS - 1], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {          // start of each bucket, longest bucket first
+        int run = 0;
+        for (int b = FR_LEN_BUCKETS - 1; b >= 0; --b) { const int c = s_cnt[b]; s_cnt[b] = run; run += c; }
+    }
+    __syncthreads();
+    for (int64_t r = tid; r < n_reads; r += blockDim.x) {
+        const int64_t b = (offsets[r + 1] - offsets[r]) >> 10;
+        order[atomicAdd(&s_cnt[b < FR_LEN_BUCKETS - 1 ? (int)b : FR_LEN_BUCKETS - 1], 1)] = (int32_t)r;
+    }
+}
+
 // ---- exclusive scan of per-read counts -> indptr (single CTA, chunked) ----
 __global__ void fr_scan_kernel(const int32_t *__restrict__ cnt, int64_t n, int64_t *indptr) {
     __shared__ long long s_warp[32];
@@ -677,6 +706,31 @@ __global__ void fr_gather_kernel(const int32_t *__restrict__ scratch, const int6
     }
 }
 
+// fr_extract_async: the same gather without a host round trip.  status[0] collects the reasons the
+// rows could not be delivered (1 scratch / 2 spill overflow of the extract pass, 4 indices too
+// small), status[1] the number of entries; nothing is written when a bit is set.
+__global__ void fr_gather_checked_kernel(const int32_t *__restrict__ scratch, const int64_t *__restrict__ read_off,
+                                         int64_t *indptr, int64_t n_reads, int32_t *indices,
+                                         int64_t cap, const unsigned long long *__restrict__ counters,
+                                         long long *status) {
+    const unsigned long long flags = counters[2];
+    const long long nnz = (long long)counters[0];
+    const long long bad = (long long)(flags & 3ull) | (nnz > cap ? 4ll : 0ll);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { status[0] |= bad; status[1] = nnz; }
+    if (bad) {      // the rows are not delivered: make them empty so that a consumer queued behind stays in bounds
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n_reads; i += (int64_t)gridDim.x * blockDim.x)
+            indptr[i] = 0;
+        return;
+    }
+    const int lane = threadIdx.x & 31;
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; r < n_reads; r += nwarps) {
+        const int64_t a = indptr[r], n = indptr[r + 1] - a, off = read_off[r];
+        for (int64_t i = lane; i < n; i += 32) indices[a + i] = scratch[off + i];
+    }
+}
+
 // kmer_searcher.cpp:327-328, 345-346, 56-86: per-feature document frequency.
 __global__ void fr_docfreq_kernel(const int32_t *__restrict__ scratch, int64_t nnz, uint32_t *docfreq) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -690,7 +744,7 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
     int64_t grid = n_reads < (int64_t)ctx->sm_count * 128 ? n_reads : (int64_t)ctx->sm_count * 128;
     if (grid < 1) grid = 1;
     typedef void (*KernelFn)(const uint8_t *, int64_t, const int64_t *, int64_t, FrTable, int32_t *, int64_t, uint32_t *,
-                             int64_t, int64_t *, int32_t *, unsigned long long *, int);
+                             int64_t, int64_t *, int32_t *, unsigned long long *, const int32_t *, int);
     static const KernelFn fns[4] = {fr_extract_kernel<false, false>, fr_extract_kernel<true, false>,
                                     fr_extract_kernel<false, true>, fr_extract_kernel<true, true>};
     static bool attr_set = false;
@@ -703,10 +757,16 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
     static const int dbg = getenv("FR_EXTRACT_DEBUG") ? atoi(getenv("FR_EXTRACT_DEBUG")) : 0;   // timing experiments only
     // a k-mer of k <= 16 fits one 32-bit word; a verified sampled library skips the filter loads
     const KernelFn fn = fns[(ctx->table.k > 16 ? 1 : 0) + (ctx->table.sampled && !(dbg & 8) ? 2 : 0)];
+    if (n_reads >= (1ll << 31)) return fr_fail(ctx, FR_ERR_ARG, "fr_extract: more than 2^31 reads in one call");
+    if (n_reads > 0) {
+        fr_kt_begin(ctx, "fr_read_order_kernel", st);
+        fr_read_order_kernel<<<1, 1024, 0, st>>>(d_offsets, n_reads, ctx->d_read_order);
+        FR_LAUNCH_CHECK(ctx, "fr_read_order_kernel");
+    }
     fr_kt_begin(ctx, "fr_extract_kernel", st);
     fn<<<(unsigned)grid, FR_THREADS, sizeof(FrExtractShared), st>>>(
         d_bases, n_bases, d_offsets, n_reads, ctx->table, ctx->d_scratch, ctx->scratch_cap, ctx->d_spill,
-        ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, dbg);
+        ctx->spill_cap, ctx->d_read_off, ctx->d_read_cnt, ctx->d_counters, ctx->d_read_order, dbg);
     FR_LAUNCH_CHECK(ctx, "fr_extract_kernel");
     return FR_OK;
 }
@@ -727,6 +787,18 @@ int fr_gather_rows(fr_ctx *ctx, int32_t *d_indices, cudaStream_t st) {
     fr_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(ctx->d_scratch, ctx->d_read_off, ctx->last_indptr, n,
                                                        d_indices);
     FR_LAUNCH_CHECK(ctx, "fr_gather_kernel");
+    return FR_OK;
+}
+
+int fr_gather_rows_checked(fr_ctx *ctx, int64_t *d_indptr, int64_t n, int32_t *d_indices, int64_t cap,
+                           long long *d_status, cudaStream_t st) {
+    int64_t blocks = (n * 32 + 255) / 256;
+    if (blocks > (int64_t)ctx->sm_count * 32) blocks = (int64_t)ctx->sm_count * 32;
+    if (blocks < 1) blocks = 1;
+    fr_kt_begin(ctx, "fr_gather_kernel", st);
+    fr_gather_checked_kernel<<<(unsigned)blocks, 256, 0, st>>>(ctx->d_scratch, ctx->d_read_off, d_indptr, n, d_indices,
+                                                               cap, ctx->d_counters, d_status);
+    FR_LAUNCH_CHECK(ctx, "fr_gather_checked_kernel");
     return FR_OK;
 }
 

@@ -57,7 +57,10 @@ constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_NS >> 3) << 17) | ((TC_
 constexpr float TC_EPS = 1.1e-3f;
 
 struct TcParams {
-    int64_t n_db, nq, q0;
+    int64_t n_db, nq, q0;       // tensor-map rows; query rows [q0, q0 + nq)
+    int64_t db0, db_end;        // database rows searched by this launch: [db0, db_end)
+    int64_t ws_off;             // workspace row of query row q0 (0 unless the workspace spans more rows)
+    int slot_base;              // first candidate buffer of a row this launch may use
     int kblks, stages;
     int64_t db_tiles, q_tiles, units;
     int n_ctas, slots, klo, khi;
@@ -253,7 +256,7 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 // among its lanes) and appends at a position it keeps in a register: the two warps of a TMEM
 // lane quadrant fill the row's buffer from opposite ends, so no atomic is needed.
 __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *ptr, int step, int &pos, float thr) {
+                                            unsigned long long *ptr, int step, int &pos, float thr, uint32_t allow) {
     // four independent 4-bit chains (a single 16-deep funnel-shift chain is pure latency)
     uint32_t m4[4];
 #pragma unroll
@@ -263,8 +266,10 @@ __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cb
         for (int j = 3; j >= 0; --j)
             m4[g] = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[4 * g + j])), m4[g], 1);
     }
-    uint32_t mask = (m4[0] | (m4[1] << 4)) | ((m4[2] << 8) | (m4[3] << 12));
-    if (ragged) {   // last database tile: columns past n_db are zero rows supplied by TMA
+    // allow = 0 for lanes without a query row: their tile rows may be memory that is not written
+    // yet (incremental search), and the sign of a NaN score is arbitrary
+    uint32_t mask = ((m4[0] | (m4[1] << 4)) | ((m4[2] << 8) | (m4[3] << 12))) & allow;
+    if (ragged) {   // last database tile of the range: columns past its end do not count
         const int64_t left = n_db - (int64_t)cbase;
         mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
     }
@@ -348,7 +353,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                             mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
                             for (int b = 0; b < TC_NS / TC_M; ++b)      // box = 64 x 128 rows
                                 tma_load_2d(sB + stage * TC_STAGE + b * TC_ABLK, &tmap, bFull + 8 * stage, kb * TC_KB,
-                                            (int)(t * TC_N + h * TC_NS + b * TC_M));
+                                            (int)(p.db0 + t * TC_N + h * TC_NS + b * TC_M));
                             if (++stage == p.stages) { stage = 0; phase ^= 1; }
                         }
                     }
@@ -410,15 +415,17 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             const int slot = cta - tc_owner(qt * p.db_tiles, p.units, p.n_ctas);
             const int64_t grow = qt * TC_M + row_in_tile;
             const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
-            const int64_t stream = (valid ? grow : 0) * p.slots + slot;
+            const int64_t wrow = valid ? grow + p.ws_off : 0;          // this row in the workspace
+            const int64_t stream = wrow * p.slots + p.slot_base + slot;
             unsigned long long *buf = p.keys + stream * CAP;
             unsigned long long *ptr = sub ? buf + CAP - 1 : buf;     // this warp's end of the row's buffer
             int mycnt = 0;
+            const uint32_t allow = valid ? 0xFFFFu : 0u;
             if (sub == 0) {
                 // start from whatever the row's other CTAs (or this CTA's earlier segment) reached
                 float t0v = INFINITY;
                 if (valid) {
-                    const unsigned int g = __ldcg(p.gthr + grow);
+                    const unsigned int g = __ldcg(p.gthr + wrow);
                     t0v = g ? ord2f(g) : -INFINITY;
                 }
                 s_thr[row_in_tile] = t0v;
@@ -430,8 +437,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 tc_fence_after();
                 const float thr = s_thr[row_in_tile];
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
-                const int64_t col0 = t * TC_N;
-                const bool ragged = col0 + TC_N > p.n_db;
+                const int64_t col0 = p.db0 + t * TC_N;
+                const bool ragged = col0 + TC_N > p.db_end;
                 // TMEM loads run two chunks ahead of the filter: the warp's 8 chunks (alternate 16-column
                 // chunks of the tile) go through two 32-register buffers
                 const int cnt_at_tile_start = mycnt;
@@ -446,8 +453,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
                     tc_ld16(taddr + (c + 4) * TC_CH, b0);
                     tc_ld16(taddr + (c + 6) * TC_CH, b1);
-                    tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
-                    tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
+                    tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();                                          // b0, b1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
@@ -455,8 +462,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                         tc_ld16(taddr + (c + 8) * TC_CH, a0);
                         tc_ld16(taddr + (c + 10) * TC_CH, a1);
                     }
-                    tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
-                    tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.n_db, ptr, step, mycnt, thr);
+                    tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
+                    tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
@@ -479,7 +486,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 // joined the row late (several slots per query tile: multi-GPU, small query sets)
                 // the slow climb from -inf.  s_thr only ever rises (it bounds everything dropped).
                 if (sub == 0 && valid) {
-                    const float gt = ord2f(__ldcg(p.gthr + grow));
+                    const float gt = ord2f(__ldcg(p.gthr + wrow));
                     if (gt > s_thr[row_in_tile]) s_thr[row_in_tile] = gt;
                 }
                 tc_quad_bar(bar_id);                     // both warps hold the same counts before either rewrites them
@@ -496,7 +503,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                                                                   p.klo, p.khi, &kept);
                         if (lane == src) {
                             if (nt > s_thr[row_in_tile]) s_thr[row_in_tile] = nt;
-                            atomicMax(p.gthr + grow, f2ord(nt));
+                            atomicMax(p.gthr + wrow, f2ord(nt));
                             s_cnt[row_in_tile] = kept;
                             s_cnt[TC_M + row_in_tile] = 0;
                         }
@@ -572,10 +579,51 @@ constexpr int RR_RES = 128;       // most candidates one row may re-rank exactly
 //  3. recompute the survivors (approximate score >= T - 2 eps; typically k + a few) in fp32 with
 //     the SAME summation order as fr_knn_exact_kernel, sort by (distance, index), emit the top k.
 // Rows that fail the certificate, or have more than RR_RES survivors, go to the exact scan.
+// T (orderable score) such that between k and k+8 of the warp's n >= k candidates score >= T
+// (more only on ties): prefix skip + bitwise search with early exit, as in K6
+__device__ uint32_t rr_kth(const unsigned long long *cand, int n, int k) {
+    const int lane = threadIdx.x & 31;
+    uint32_t mx = 0, mn = 0xFFFFFFFFu;
+    for (int i = lane; i < n; i += 32) { const uint32_t h = (uint32_t)(cand[i] >> 32); mx = max(mx, h); mn = min(mn, h); }
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    mn = __reduce_min_sync(0xFFFFFFFFu, mn);
+    uint32_t T = mn;
+    if (n > k + 8 && mx != mn) {
+        const int b0 = 31 - __clz(mx ^ mn);
+        T = b0 == 31 ? 0u : (mx >> (b0 + 1)) << (b0 + 1);
+        for (int b = b0; b >= 0; --b) {
+            const uint32_t cd = T | (1u << b);
+            int c = 0;
+            for (int i = lane; i < n; i += 32) c += (uint32_t)(cand[i] >> 32) >= cd;
+            c = __reduce_add_sync(0xFFFFFFFFu, c);
+            if (c >= k) { T = cd; if (c <= k + 8) break; }
+        }
+    }
+    return T;
+}
+
+// keeps the candidates whose score is >= Lo at the front of cand; returns how many
+__device__ int rr_compact(unsigned long long *cand, int n, uint32_t Lo) {
+    const int lane = threadIdx.x & 31;
+    int m = 0;
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const unsigned long long key = i < n ? cand[i] : 0ull;
+        const bool kp = i < n && (uint32_t)(key >> 32) >= Lo;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
+        __syncwarp();
+        if (kp) cand[m + __popc(bal & ((1u << lane) - 1))] = key;   // never passes the read position
+        m += __popc(bal);
+        __syncwarp();
+    }
+    return m;
+}
+
 __global__ void __launch_bounds__(RR_WARPS * 32)
 fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
                      int64_t nq, int k, int slots, int cap, int max_n, const unsigned long long *__restrict__ keys,
-                     const int *__restrict__ counts, const float *__restrict__ thrs, int32_t *__restrict__ out_idx,
+                     const int *__restrict__ counts, const float *__restrict__ thrs,
+                     const unsigned int *__restrict__ gthr, int32_t *__restrict__ out_idx,
                      float *__restrict__ out_dist, int32_t *__restrict__ fb_rows, unsigned long long *fb_count) {
     extern __shared__ __align__(16) unsigned char rr_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -592,54 +640,63 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
         int n = 0;
         float tau = -INFINITY;      // largest final threshold of a buffer that ever dropped something
         bool ok = true;
-        for (int s = 0; s < slots; ++s) {
+        // One of the row's buffers holds >= klo (> k) candidates at or above the shared threshold G
+        // (K6 raises it only after such a selection), so the k-th best score is >= G and a candidate
+        // below G - 2 eps can neither be a survivor nor move T: it is dropped while merging.
+        // When the merge area fills up (a row with many buffers: incremental search) the same argument
+        // is applied to the k-th best score merged so far.
+        // Rows whose buffers fit as they are (the usual case of a one-shot search) are copied plainly.
+        int total = 0;
+        for (int s = lane; s < slots; s += 32) { const int cc = counts[row * slots + s]; total += (cc & 0xFFFF) + (cc >> 16); }
+        total = __reduce_add_sync(0xFFFFFFFFu, total);
+        const unsigned int g = total > max_n ? gthr[row] : 0u;
+        uint32_t Lg = g ? f2ord(ord2f(g) - 2.0f * TC_EPS) : 0u;
+        if (total <= max_n) {
+            for (int s = 0; s < slots; ++s) {
+                const int cc = counts[row * slots + s];
+                const int c0 = cc & 0xFFFF, c = c0 + (cc >> 16);
+                if (c == 0) continue;
+                tau = fmaxf(tau, thrs[row * slots + s]);
+                const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
+                for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0)));
+                n += c;
+            }
+        } else
+        for (int s = 0; s < slots && ok; ++s) {
             const int cc = counts[row * slots + s];
             const int c0 = cc & 0xFFFF, c = c0 + (cc >> 16);      // front part, total (rest sits at the end)
             if (c == 0) continue;
             tau = fmaxf(tau, thrs[row * slots + s]);
-            if (n + c > max_n) { ok = false; break; }
             const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
-            for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0)));
-            n += c;
+            for (int i0 = 0; i0 < c; i0 += 32) {
+                const int i = i0 + lane;
+                const unsigned long long key = i < c ? __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0))) : 0ull;
+                bool kp = i < c && (uint32_t)(key >> 32) >= Lg;
+                unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
+                if (n + __popc(bal) > max_n && n >= k) {
+                    __syncwarp();
+                    const uint32_t lo2 = f2ord(ord2f(rr_kth(cand, n, k)) - 2.0f * TC_EPS);
+                    if (lo2 > Lg) { Lg = lo2; n = rr_compact(cand, n, Lg); }
+                    kp = i < c && (uint32_t)(key >> 32) >= Lg;
+                    bal = __ballot_sync(0xFFFFFFFFu, kp);
+                }
+                const int add = __popc(bal);
+                if (n + add > max_n) { ok = false; break; }
+                if (kp) cand[n + __popc(bal & ((1u << lane) - 1))] = key;
+                n += add;
+            }
         }
         __syncwarp();
         ok = ok && n >= k;
         // ---- 2. T: between k and k+8 candidates score >= T (prefix skip + early exit, as in K6)
         uint32_t T = 0;
-        if (ok) {
-            uint32_t mx = 0, mn = 0xFFFFFFFFu;
-            for (int i = lane; i < n; i += 32) { const uint32_t h = (uint32_t)(cand[i] >> 32); mx = max(mx, h); mn = min(mn, h); }
-            mx = __reduce_max_sync(0xFFFFFFFFu, mx);
-            mn = __reduce_min_sync(0xFFFFFFFFu, mn);
-            T = mn;
-            if (n > k + 8 && mx != mn) {
-                const int b0 = 31 - __clz(mx ^ mn);
-                T = b0 == 31 ? 0u : (mx >> (b0 + 1)) << (b0 + 1);
-                for (int b = b0; b >= 0; --b) {
-                    const uint32_t cd = T | (1u << b);
-                    int c = 0;
-                    for (int i = lane; i < n; i += 32) c += (uint32_t)(cand[i] >> 32) >= cd;
-                    c = __reduce_add_sync(0xFFFFFFFFu, c);
-                    if (c >= k) { T = cd; if (c <= k + 8) break; }
-                }
-            }
-        }
+        if (ok) T = rr_kth(cand, n, k);
         // ---- survivors: approximate score >= T - 2 eps, compacted to the front of cand
         int m = 0;
         float cut = -INFINITY;
         if (ok) {
             cut = ord2f(T) - 2.0f * TC_EPS;
-            const uint32_t Lo = f2ord(cut);
-            for (int i0 = 0; i0 < n; i0 += 32) {
-                const int i = i0 + lane;
-                const unsigned long long key = i < n ? cand[i] : 0ull;
-                const bool kp = i < n && (uint32_t)(key >> 32) >= Lo;
-                const unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
-                __syncwarp();
-                if (kp) cand[m + __popc(bal & ((1u << lane) - 1))] = key;   // never passes the read position
-                m += __popc(bal);
-                __syncwarp();
-            }
+            m = rr_compact(cand, n, f2ord(cut));
             // certificate: every buffer's dropped candidates scored <= its threshold < T - 2 eps
             ok = m <= RR_RES && (tau == -INFINITY || tau < cut);
         }
@@ -713,71 +770,57 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-template <int CAP>
-int tc_run(fr_ctx *ctx, const CUtensorMap &tmap, const TcParams &p, size_t smem, const float *d_En,
-           const float *d_norms, int D, int k, int32_t *d_idx, float *d_dist, int32_t *fb_rows,
-           unsigned long long *fb_count, cudaStream_t st) {
-    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
-    fr_knn_tc_kernel<CAP><<<p.n_ctas, TC_THREADS, smem, st>>>(tmap, p);
-    FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
-    {   // K6 read only the fp16 copy; the fp32 rows (K7, fallback) may still be arriving (all-gather)
-        int rcw = fr_knn_wait_rows(ctx, st);
-        if (rcw) return rcw;
-    }
-    int max_n = p.slots * CAP;                         // keys one row can hold across its buffers
-    if (max_n > 4096) max_n = 4096;                    // (rows beyond it go to the exact scan)
-    const size_t rsmem = (size_t)RR_WARPS * ((size_t)max_n * 8 + (size_t)RR_RES * 8);
-    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
-    int64_t blocks = (p.nq + RR_WARPS - 1) / RR_WARPS;
-    if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
-    fr_kt_begin(ctx, "fr_knn_rerank_kernel", st);
-    fr_knn_rerank_kernel<<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
-        d_En, d_norms, p.n_db, D, p.q0, p.nq, k, p.slots, CAP, max_n, p.keys, p.counts, p.thrs, d_idx, d_dist, fb_rows,
-        fb_count);
-    FR_LAUNCH_CHECK(ctx, "fr_knn_rerank_kernel");
-    return FR_OK;
+// ---------------------------------------------------------------- host side
+struct TcSetup {            // what every K6 launch of one search shares
+    TcParams p{};           // keys/counts/thrs/gthr/norms, kblks, stages, klo, khi, n_db; slots = buffers per row
+    CUtensorMap tmap;
+    size_t smem = 0;
+    int cap = 0;
+    int32_t *fb_rows = nullptr;
+    unsigned long long *fb_count = nullptr;
+};
+
+bool tc_shape_ok(int64_t n_db, int D, int Dp, int k) {
+    return !(Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N);
 }
 
-}  // namespace
-
-int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
-                     int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
-    // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
-    if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N) {
-        int rcw = fr_knn_wait_rows(ctx, st);
-        if (rcw) return rcw;
-    }
-    if (Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N)
-        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
-    EncodeTiledFn encode = get_encode_fn();
-    if (!encode) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled is not available");
-    // selection window (how many candidates a compaction keeps) and the physical buffer size: a
-    // row may gain a whole tile (256 columns) between compactions
-    const int win = k <= 32 ? 128 : (k <= 64 ? 256 : 512);
-    const int cap = win <= 256 ? 512 : 1024;
-
-    TcParams p{};
-    p.n_db = n_db; p.nq = nq; p.q0 = q0;
-    p.kblks = Dp / TC_KB;
-    const size_t fixed = 1024 + 256 + TC_STASH + TC_ROWST + (size_t)p.kblks * TC_ABLK;
-    int stages = (int)((232448 - fixed) / TC_STAGE);
-    p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
-    const size_t smem = fixed + (size_t)p.stages * TC_STAGE;
-    p.db_tiles = (n_db + TC_N - 1) / TC_N;
+// the persistent-CTA split of nq query rows x ndb database rows; returns the most CTAs that share
+// one query tile (= candidate buffers a row needs for this launch; same arithmetic as tc_owner)
+int tc_geometry(const fr_ctx *ctx, TcParams &p, int64_t nq, int64_t ndb) {
+    p.db_tiles = (ndb + TC_N - 1) / TC_N;
     p.q_tiles = (nq + TC_M - 1) / TC_M;
     p.units = p.db_tiles * p.q_tiles;
     int64_t n_ctas = ctx->sm_count;
     if (n_ctas > 4 * p.q_tiles) n_ctas = 4 * p.q_tiles;
     if (n_ctas > p.units) n_ctas = p.units;
     p.n_ctas = (int)n_ctas;
-    p.slots = 1;   // most CTAs that share one query tile (exact, same arithmetic as tc_owner)
+    int slots = 1;
     for (int64_t qt = 0; qt < p.q_tiles; ++qt) {
         const int64_t a = ((qt * p.db_tiles + 1) * n_ctas - 1) / p.units;
         const int64_t b = (((qt + 1) * p.db_tiles) * n_ctas - 1) / p.units;
-        if ((int)(b - a + 1) > p.slots) p.slots = (int)(b - a + 1);
+        if ((int)(b - a + 1) > slots) slots = (int)(b - a + 1);
     }
-    if (p.slots > TC_MAX_SLOTS) return fr_fail(ctx, FR_ERR_STATE, "fr_knn: internal slot bound exceeded");
+    return slots;
+}
+
+// everything but the geometry: selection window, smem budget, workspace for ws_rows rows x slots
+// buffers (cleared), tensor map over the whole fp16 copy
+int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, int64_t n_db, int Dp, int k,
+             int64_t ws_rows, int slots, cudaStream_t st) {
+    EncodeTiledFn encode = get_encode_fn();
+    if (!encode) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled is not available");
+    // selection window (how many candidates a compaction keeps) and the physical buffer size: a
+    // row may gain a whole tile (256 columns) between compactions
+    const int win = k <= 32 ? 128 : (k <= 64 ? 256 : 512);
+    S.cap = win <= 256 ? 512 : 1024;
+    TcParams &p = S.p;
+    p.n_db = n_db;
+    p.kblks = Dp / TC_KB;
+    const size_t fixed = 1024 + 256 + TC_STASH + TC_ROWST + (size_t)p.kblks * TC_ABLK;
+    int stages = (int)((232448 - fixed) / TC_STAGE);
+    p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
+    S.smem = fixed + (size_t)p.stages * TC_STAGE;
+    p.slots = slots;
     // a compaction keeps between klo and khi keys: enough beyond k that the k-th and the klo-th
     // score are normally more than 2 eps apart (the K7 certificate), few enough that the running
     // threshold stays tight (hits per row grow with the kept count)
@@ -787,10 +830,10 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     if (const char *e = getenv("FR_KNN_KHI")) p.khi = atoi(e);
     p.norms = d_norms;
 
-    // workspace: keys | counts | thrs | fallback rows | fallback counter
-    const int64_t streams = nq * p.slots;
-    const size_t keys_b = (size_t)streams * cap * 8, cnt_b = ((size_t)streams * 4 + 15) & ~(size_t)15;
-    const size_t rows_b = ((size_t)nq * 4 + 15) & ~(size_t)15;
+    // workspace: keys | counts | thrs | fallback rows | shared thresholds | fallback counter
+    const int64_t streams = ws_rows * slots;
+    const size_t keys_b = (size_t)streams * S.cap * 8, cnt_b = ((size_t)streams * 4 + 15) & ~(size_t)15;
+    const size_t rows_b = ((size_t)ws_rows * 4 + 15) & ~(size_t)15;
     const size_t need = keys_b + 2 * cnt_b + 2 * rows_b + 16;
     int rc = fr_ensure(ctx, &ctx->d_knn_ws, &ctx->knn_ws_cap, (int64_t)need, "kNN workspace");
     if (rc) return rc;
@@ -798,61 +841,252 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     p.keys = (unsigned long long *)ws;
     p.counts = (int *)(ws + keys_b);
     p.thrs = (float *)(ws + keys_b + cnt_b);
-    int32_t *fb_rows = (int32_t *)(ws + keys_b + 2 * cnt_b);
-    unsigned long long *fb_count = (unsigned long long *)(ws + need - 16);
+    S.fb_rows = (int32_t *)(ws + keys_b + 2 * cnt_b);
+    S.fb_count = (unsigned long long *)(ws + need - 16);
     p.gthr = (unsigned int *)(ws + keys_b + 2 * cnt_b + rows_b);
     FR_CUDA(ctx, cudaMemsetAsync(p.gthr, 0, rows_b, st));          // 0 orders below every float
     FR_CUDA(ctx, cudaMemsetAsync(p.counts, 0, cnt_b, st));
-    FR_CUDA(ctx, cudaMemsetAsync(fb_count, 0, 16, st));
+    FR_CUDA(ctx, cudaMemsetAsync(S.fb_count, 0, 16, st));
 
-    static const bool dbg_env = getenv("FR_KNN_DEBUG") != nullptr;
-    static unsigned long long *d_dbg = nullptr;
-    if (dbg_env) {
-        if (!d_dbg) cudaMalloc(&d_dbg, 128);
-        cudaMemsetAsync(d_dbg, 0, 128, st);
-        p.dbg = d_dbg;
-    }
-    CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)Dp, (cuuint64_t)n_db};
     const cuuint64_t gstr[1] = {(cuuint64_t)Dp * 2};
     const cuuint32_t box[2] = {TC_KB, TC_M};
     const cuuint32_t estr[2] = {1, 1};
-    CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(d_Eh), gdim, gstr, box, estr,
+    CUresult cr = encode(&S.tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(d_Eh), gdim, gstr, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return fr_fail(ctx, FR_ERR_CUDA, "fr_knn: cuTensorMapEncodeTiled failed");
+    return FR_OK;
+}
 
-    if (cap == 512)
-        rc = tc_run<512>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
-    else
-        rc = tc_run<1024>(ctx, tmap, p, smem, d_En, d_norms, D, k, d_idx, d_dist, fb_rows, fb_count, st);
-    if (rc) return rc;
-    if (dbg_env) {
-        unsigned long long h[16];
-        cudaStreamSynchronize(st);
-        cudaMemcpy(h, d_dbg, 128, cudaMemcpyDeviceToHost);
-        const double n = p.n_ctas;
-        fprintf(stderr, "[fr_knn dbg] per-CTA Mcycles: life %.2f | producer wait-empty %.2f | mma wait-data %.2f wait-tmem %.2f"
-                        " | epilogue(avg per warp) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
-                h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / (4e6 * TC_EPQ), h[4] / n / (4e6 * TC_EPQ),
-                (double)p.units / n);
-        const double ew = n * 4e6 * TC_EPQ;
-        fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f (%.0f compactions per CTA)\n",
-                h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
-        fprintf(stderr, "[fr_knn dbg] hits per query row %.0f | per warp and tile: %.1f hits, largest per-lane count %.2f\n",
-                (double)h[13] / (double)p.nq, (double)h[13] / ((double)p.units * 4 * TC_EPQ),
-                (double)h[14] / ((double)p.units * 4 * TC_EPQ));
+// one K6 launch: query rows [q0, q0 + nq) against database rows [db0, db_end); p carries the geometry
+int tc_launch_k6(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st) {
+    fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
+    if (S.cap == 512) {
+        FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+        fr_knn_tc_kernel<512><<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
+    } else {
+        FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+        fr_knn_tc_kernel<1024><<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
     }
+    FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
+    return FR_OK;
+}
+
+// K7 over workspace rows [0, nq) (= query rows q0 ...), then the exact paths for uncertified rows
+int tc_finish(fr_ctx *ctx, const TcSetup &S, const float *d_En, const float *d_norms, int D, int64_t q0, int64_t nq,
+              int k, int max_keys, int32_t *d_idx, float *d_dist, cudaStream_t st) {
+    const TcParams &p = S.p;
+    {   // K6 read only the fp16 copy; the fp32 rows (K7, fallback) may still be arriving (all-gather)
+        int rcw = fr_knn_wait_rows(ctx, st);
+        if (rcw) return rcw;
+    }
+    // keys of one row K7 merges in shared memory (after dropping those below the shared threshold);
+    // rows with more go to the exact paths.  The bound sets K7's occupancy: 8 bytes per key and warp.
+    int max_n = p.slots * S.cap;
+    if (max_n > max_keys) max_n = max_keys;
+    const size_t rsmem = (size_t)RR_WARPS * ((size_t)max_n * 8 + (size_t)RR_RES * 8);
+    FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
+    int64_t blocks = (nq + RR_WARPS - 1) / RR_WARPS;
+    if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
+    fr_kt_begin(ctx, "fr_knn_rerank_kernel", st);
+    fr_knn_rerank_kernel<<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
+        d_En, d_norms, p.n_db, D, q0, nq, k, p.slots, S.cap, max_n, p.keys, p.counts, p.thrs, p.gthr, d_idx, d_dist,
+        S.fb_rows, S.fb_count);
+    FR_LAUNCH_CHECK(ctx, "fr_knn_rerank_kernel");
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)
     // ... the first few in parallel over the database (one warp per database row, then a block-wide
     // exact selection per query), any beyond that by the one-warp-per-query scan
     int covered = 0;
-    rc = fr_knn_fallback_launch(ctx, d_En, d_norms, n_db, D, q0, k, fb_rows, fb_count, d_idx, d_dist, &covered, st);
+    int rc = fr_knn_fallback_launch(ctx, d_En, d_norms, p.n_db, D, q0, k, S.fb_rows, S.fb_count, d_idx, d_dist,
+                                    &covered, st);
     if (rc) return rc;
-    rc = fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, fb_rows, fb_count, covered, d_idx, d_dist, st);
+    rc = fr_knn_exact_launch(ctx, d_En, d_norms, p.n_db, D, q0, nq, k, S.fb_rows, S.fb_count, covered, d_idx, d_dist,
+                             st);
     if (rc) return rc;
-    FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[4], fb_count, 8, cudaMemcpyDeviceToHost, st));
+    FR_CUDA(ctx, cudaMemcpyAsync(&ctx->h_counters[4], S.fb_count, 8, cudaMemcpyDeviceToHost, st));
     ctx->knn_fb_pending = true;
     ctx->knn_fb_stream = st;
     return FR_OK;
+}
+
+unsigned long long *tc_debug_buffer(cudaStream_t st) {   // FR_KNN_DEBUG=1: per-role cycle counters
+    static const bool on = getenv("FR_KNN_DEBUG") != nullptr;
+    static unsigned long long *d_dbg = nullptr;
+    if (!on) return nullptr;
+    if (!d_dbg) cudaMalloc(&d_dbg, 128);
+    cudaMemsetAsync(d_dbg, 0, 128, st);
+    return d_dbg;
+}
+
+void tc_debug_report(const TcParams &p, unsigned long long *d_dbg, cudaStream_t st) {
+    unsigned long long h[16];
+    cudaStreamSynchronize(st);
+    cudaMemcpy(h, d_dbg, 128, cudaMemcpyDeviceToHost);
+    const double n = p.n_ctas;
+    fprintf(stderr, "[fr_knn dbg] per-CTA Mcycles: life %.2f | producer wait-empty %.2f | mma wait-data %.2f wait-tmem %.2f"
+                    " | epilogue(avg per warp) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
+            h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / (4e6 * TC_EPQ), h[4] / n / (4e6 * TC_EPQ),
+            (double)p.units / n);
+    const double ew = n * 4e6 * TC_EPQ;
+    fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f (%.0f compactions per CTA)\n",
+            h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
+    fprintf(stderr, "[fr_knn dbg] hits per query row %.0f | per warp and tile: %.1f hits, largest per-lane count %.2f\n",
+            (double)h[13] / (double)p.nq, (double)h[13] / ((double)p.units * 4 * TC_EPQ),
+            (double)h[14] / ((double)p.units * 4 * TC_EPQ));
+}
+
+// state of an incremental search (fr_knn_inc_*)
+struct TcInc {
+    TcSetup S;
+    const float *En = nullptr, *norms = nullptr;
+    int D = 0, k = 0;
+    std::vector<int64_t> bounds;       // cumulative row bounds of the phases
+    std::vector<int> base_b;           // first buffer of the (earlier rows x new rows) launch of phase j
+    int next_phase = 0;
+};
+
+void tc_inc_free(void *q) { delete static_cast<TcInc *>(q); }
+
+}  // namespace
+
+int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db, int D,
+                     int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
+    // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
+    if (!tc_shape_ok(n_db, D, Dp, k)) {
+        int rcw = fr_knn_wait_rows(ctx, st);
+        if (rcw) return rcw;
+        return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
+    }
+    TcSetup S;
+    TcParams geo{};
+    const int slots = tc_geometry(ctx, geo, nq, n_db);
+    if (slots > TC_MAX_SLOTS) return fr_fail(ctx, FR_ERR_STATE, "fr_knn: internal slot bound exceeded");
+    int rc = tc_setup(ctx, S, d_Eh, d_norms, n_db, Dp, k, nq, slots, st);
+    if (rc) return rc;
+    TcParams p = S.p;
+    tc_geometry(ctx, p, nq, n_db);
+    p.nq = nq; p.q0 = q0;
+    p.db0 = 0; p.db_end = n_db;
+    p.ws_off = 0; p.slot_base = 0;
+
+    p.dbg = tc_debug_buffer(st);
+    rc = tc_launch_k6(ctx, S, p, st);
+    if (rc) return rc;
+    if (p.dbg) tc_debug_report(p, p.dbg, st);
+    return tc_finish(ctx, S, d_En, d_norms, D, q0, nq, k, 4096, d_idx, d_dist, st);
+}
+
+// ---------------------------------------------------------------- incremental all-vs-all search
+// The database arrives in row ranges (the reads of later chunks are still crossing PCIe, or being
+// extracted).  Phase j needs rows [0, bounds[j+1]) and runs two K6 launches: the new rows as queries
+// against everything present, and the earlier rows as queries against the new rows only -- after
+// the last phase every (query, database row) pair has been scored exactly once.  Candidate buffers,
+// counts and the shared per-row thresholds persist across launches (a row's later launches start
+// from the threshold it has already reached), each launch appends to buffers of its own, and K7
+// runs once at the end over all of them: the same certificate, hence the same bits, as fr_knn.
+extern "C" int fr_knn_inc_begin(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db,
+                                int D, int Dp, int k, int n_phases, const int64_t *bounds, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    if (!d_En || !d_Eh || !d_norms || !bounds || n_phases < 1 || n_phases > 64 || n_db <= 0 || D <= 0 || Dp < D ||
+        (Dp % 64) != 0 || k < 1)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_knn_inc_begin: bad argument");
+    if (bounds[0] != 0 || bounds[n_phases] != n_db)
+        return fr_fail(ctx, FR_ERR_ARG, "fr_knn_inc_begin: bounds must run from 0 to n_db");
+    for (int j = 0; j < n_phases; ++j)
+        if (bounds[j + 1] < bounds[j]) return fr_fail(ctx, FR_ERR_ARG, "fr_knn_inc_begin: bounds must not decrease");
+    if (!tc_shape_ok(n_db, D, Dp, k))
+        return fr_fail(ctx, FR_ERR_ARG, "fr_knn_inc_begin: shape not covered by the tensor-core path (use fr_knn)");
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (ctx->knn_inc) { tc_inc_free(ctx->knn_inc); ctx->knn_inc = nullptr; }
+    TcInc *inc = new TcInc();
+    ctx->knn_inc = inc;
+    ctx->knn_inc_free = tc_inc_free;
+    inc->En = d_En; inc->norms = d_norms; inc->D = D; inc->k = k;
+    inc->bounds.assign(bounds, bounds + n_phases + 1);
+    inc->base_b.assign(n_phases, 0);
+    // buffers per row: the widest (new rows x all) launch, plus those of every (earlier x new) launch
+    int slots_a = 1, total = 0;
+    TcParams geo{};
+    for (int j = 0; j < n_phases; ++j) {
+        const int64_t a = bounds[j], b = bounds[j + 1];
+        if (b == a) continue;
+        const int sa = tc_geometry(ctx, geo, b - a, b);
+        if (sa > slots_a) slots_a = sa;
+    }
+    total = slots_a;
+    for (int j = 1; j < n_phases; ++j) {
+        const int64_t a = bounds[j], b = bounds[j + 1];
+        inc->base_b[j] = total;
+        if (b == a || a == 0) continue;
+        total += tc_geometry(ctx, geo, a, b - a);
+    }
+    ctx->knn_fallback_rows = 0;
+    ctx->knn_fb_pending = false;
+    int rc = tc_setup(ctx, inc->S, d_Eh, d_norms, n_db, Dp, k, n_db, total, st);
+    if (rc) { tc_inc_free(inc); ctx->knn_inc = nullptr; return rc; }
+    return FR_OK;
+}
+
+extern "C" int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    TcInc *inc = static_cast<TcInc *>(ctx->knn_inc);
+    if (!inc) return fr_fail(ctx, FR_ERR_STATE, "fr_knn_inc_phase: no search in progress (call fr_knn_inc_begin)");
+    if (j != inc->next_phase || j >= (int)inc->bounds.size() - 1)
+        return fr_fail(ctx, FR_ERR_STATE, "fr_knn_inc_phase: phases must be run once each, in order");
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t a = inc->bounds[j], b = inc->bounds[j + 1];
+    inc->next_phase = j + 1;
+    if (b == a) return FR_OK;
+    {   // new rows x everything present
+        TcParams p = inc->S.p;
+        tc_geometry(ctx, p, b - a, b);
+        p.q0 = a; p.nq = b - a;
+        p.db0 = 0; p.db_end = b;
+        p.ws_off = a; p.slot_base = 0;
+        p.dbg = tc_debug_buffer(st);
+        int rc = tc_launch_k6(ctx, inc->S, p, st);
+        if (rc) return rc;
+        if (p.dbg) {
+            fprintf(stderr, "[fr_knn dbg] phase %d, new rows x all: %lld x %lld, %d CTAs\n", j, (long long)p.nq,
+                    (long long)(p.db_end - p.db0), p.n_ctas);
+            tc_debug_report(p, p.dbg, st);
+        }
+    }
+    if (a > 0) {   // earlier rows x new rows
+        TcParams p = inc->S.p;
+        tc_geometry(ctx, p, a, b - a);
+        p.q0 = 0; p.nq = a;
+        p.db0 = a; p.db_end = b;
+        p.ws_off = 0; p.slot_base = inc->base_b[j];
+        p.dbg = tc_debug_buffer(st);
+        int rc = tc_launch_k6(ctx, inc->S, p, st);
+        if (rc) return rc;
+        if (p.dbg) {
+            fprintf(stderr, "[fr_knn dbg] phase %d, earlier rows x new: %lld x %lld, %d CTAs\n", j, (long long)p.nq,
+                    (long long)(p.db_end - p.db0), p.n_ctas);
+            tc_debug_report(p, p.dbg, st);
+        }
+    }
+    return FR_OK;
+}
+
+extern "C" int fr_knn_inc_finish(fr_ctx *ctx, int32_t *d_idx, float *d_dist, void *stream) {
+    if (!ctx) return FR_ERR_ARG;
+    TcInc *inc = static_cast<TcInc *>(ctx->knn_inc);
+    if (!inc) return fr_fail(ctx, FR_ERR_STATE, "fr_knn_inc_finish: no search in progress");
+    if (!d_idx || !d_dist) return fr_fail(ctx, FR_ERR_ARG, "fr_knn_inc_finish: bad argument");
+    if (inc->next_phase != (int)inc->bounds.size() - 1)
+        return fr_fail(ctx, FR_ERR_STATE, "fr_knn_inc_finish: not every phase has run");
+    FR_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t n_db = inc->S.p.n_db;
+    // a row has many buffers here, most of them nearly empty once its threshold is up: two buffers'
+    // worth of keys is what a one-shot search of the same size merges
+    int rc = tc_finish(ctx, inc->S, inc->En, inc->norms, inc->D, 0, n_db, inc->k, 2 * inc->S.cap, d_idx, d_dist,
+                       (cudaStream_t)stream);
+    tc_inc_free(inc);
+    ctx->knn_inc = nullptr;
+    return rc;
 }

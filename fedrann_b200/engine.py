@@ -216,6 +216,20 @@ class Engine:
         check(self.h, self.L.fr_extract_fill(self.h, _ptr(indices), _stream()), "fr_extract_fill")
         return indptr, indices[: nnz.value]
 
+    def extract_async(self, bases: torch.Tensor, offsets: torch.Tensor, indices: torch.Tensor, status: torch.Tensor):
+        """fr_extract_async: no host synchronisation.  indices: int32 buffer (its size is the capacity);
+        status: int64[2] on the device, zeroed by the caller -- after the stream has drained
+        status[0] != 0 means the rows did not fit and nothing was written, status[1] = non-zeros.
+        -> indptr int64[R+1]."""
+        assert bases.dtype == torch.uint8 and offsets.dtype == torch.int64
+        assert indices.dtype == torch.int32 and status.dtype == torch.int64 and status.numel() == 2
+        R = offsets.numel() - 1
+        indptr = torch.empty(R + 1, dtype=torch.int64, device=bases.device)
+        check(self.h, self.L.fr_extract_async(self.h, _ptr(bases), bases.numel(), _ptr(offsets), R, _ptr(indptr),
+                                              _ptr(indices), indices.numel(), _ptr(status), _stream()),
+              "fr_extract_async")
+        return indptr
+
     # -- K4 --------------------------------------------------------------
     def upload_projection(self, P_csr):
         """scipy CSR (F x D) fp32 -> device triple."""
@@ -237,31 +251,78 @@ class Engine:
         return E
 
     # -- K5 --------------------------------------------------------------
-    def normalize(self, E: torch.Tensor):
+    def normalize(self, E: torch.Tensor, out=None):
+        """out: (En, Eh, norms) row slices to write into (contiguous, same row count as E)."""
         N, D = E.shape
         Dp = (D + 63) // 64 * 64
-        En = torch.empty_like(E)
-        Eh = torch.empty((N, Dp), dtype=torch.float16, device=E.device)
-        norms = torch.empty(N, dtype=torch.float32, device=E.device)
+        if out is not None:
+            En, Eh, norms = out
+            assert En.shape == E.shape and Eh.shape == (N, Dp) and norms.shape == (N,)
+            assert En.is_contiguous() and Eh.is_contiguous() and norms.is_contiguous()
+        else:
+            En = torch.empty_like(E)
+            Eh = torch.empty((N, Dp), dtype=torch.float16, device=E.device)
+            norms = torch.empty(N, dtype=torch.float32, device=E.device)
+        if N == 0:
+            return En, Eh, norms
         check(self.h, self.L.fr_normalize(self.h, _ptr(E), N, D, Dp, _ptr(En), _ptr(Eh), _ptr(norms), _stream()),
               "fr_normalize")
         return En, Eh, norms
 
     # -- K6 + K7 ---------------------------------------------------------
-    def knn(self, En, Eh, norms, k: int, q0: int = 0, nq: int | None = None, mode: int = 0, rows_ready=None):
+    def knn(self, En, Eh, norms, k: int, q0: int = 0, nq: int | None = None, mode: int = 0, rows_ready=None,
+            out=None):
         """rows_ready: a torch.cuda.Event after which En is complete (it may still be arriving from
-        an all-gather on another stream); the tensor-core pass does not wait for it."""
+        an all-gather on another stream); the tensor-core pass does not wait for it.
+        out: (idx int32 [nq, k], dist fp32 [nq, k]) contiguous tensors to write into -- device tensors,
+        or PINNED host tensors (the kernels then write the neighbour lists straight into host memory
+        over PCIe while they run, instead of a copy afterwards)."""
         N, D = En.shape
         if rows_ready is not None:
             check(self.h, self.L.fr_knn_rows_ready_after(self.h, C.c_void_p(rows_ready.cuda_event)),
                   "fr_knn_rows_ready_after")
         nq = N - q0 if nq is None else nq
-        idx = torch.empty((nq, k), dtype=torch.int32, device=En.device)
-        dist = torch.empty((nq, k), dtype=torch.float32, device=En.device)
+        idx, dist = self._knn_out(out, nq, k, En.device)
         Dp = Eh.shape[1] if Eh is not None else D
         check(self.h, self.L.fr_knn(self.h, _ptr(En), _ptr(Eh), _ptr(norms), N, D, Dp, q0, nq, k, mode,
                                     _ptr(idx), _ptr(dist), _stream()), "fr_knn")
         return idx, dist
+
+    def knn_inc_begin(self, En, Eh, norms, k: int, bounds):
+        """Incremental all-vs-all search: En/Eh/norms are the full-size arrays, bounds the cumulative
+        row counts of the phases (fr_knn_inc_begin).  Raises FedrannError for shapes the tensor-core
+        path does not cover."""
+        N, D = En.shape
+        b = np.ascontiguousarray(np.asarray(bounds, dtype=np.int64))
+        self._inc = (N, k, En.device)
+        check(self.h, self.L.fr_knn_inc_begin(self.h, _ptr(En), _ptr(Eh), _ptr(norms), N, D, Eh.shape[1], k,
+                                              len(b) - 1, b.ctypes.data_as(C.c_void_p), _stream()), "fr_knn_inc_begin")
+
+    def knn_inc_phase(self, j: int):
+        check(self.h, self.L.fr_knn_inc_phase(self.h, j, _stream()), "fr_knn_inc_phase")
+
+    @staticmethod
+    def _knn_out(out, nq, k, dev):
+        if out is None:
+            return (torch.empty((nq, k), dtype=torch.int32, device=dev),
+                    torch.empty((nq, k), dtype=torch.float32, device=dev))
+        idx, dist = out
+        assert idx.dtype == torch.int32 and dist.dtype == torch.float32
+        assert tuple(idx.shape) == (nq, k) and tuple(dist.shape) == (nq, k)
+        assert idx.is_contiguous() and dist.is_contiguous()
+        assert (idx.is_cuda or idx.is_pinned()) and (dist.is_cuda or dist.is_pinned())
+        return idx, dist
+
+    def knn_inc_finish(self, out=None):
+        N, k, dev = self._inc
+        idx, dist = self._knn_out(out, N, k, dev)
+        check(self.h, self.L.fr_knn_inc_finish(self.h, _ptr(idx), _ptr(dist), _stream()), "fr_knn_inc_finish")
+        return idx, dist
+
+    @staticmethod
+    def knn_inc_supported(N: int, D: int, k: int) -> bool:
+        """shapes fr_knn_inc_begin accepts (the others go through fr_knn, which has the exact scan)"""
+        return D <= 512 and k <= 128 and N >= 2 * k and N < 2 ** 31 - 256
 
     @property
     def knn_fallback_rows(self) -> int:

@@ -112,29 +112,56 @@ class HostBuffers:
 
 
 def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *, mode: int = 0, group=None,
-                      timers: StageTimes | None = None, chunks: int = 8, rows_per_rank=None) -> HotPathResult:
+                      timers: StageTimes | None = None, chunks=(0.15, 0.3, 0.45, 0.6, 0.8), rows_per_rank=None,
+                      knn_overlap: bool = True, knn_phase_ends=None, async_extract: bool = True,
+                      direct_out: bool = True, trace: list | None = None) -> HotPathResult:
     """The call a host program makes: reads in pinned host memory -> device ->
     extract/project/kNN -> neighbour lists back in pinned host memory.  Returns
     after the results have landed.
 
-    The reads cross PCIe in `chunks` pieces on a copy stream while the compute
-    stream extracts and projects the pieces that have arrived (reads are
-    independent); the kNN starts when the last piece is projected."""
+    The reads cross PCIe in `chunks` pieces (an int: equal pieces; a sequence: the
+    cumulative fractions of the bases at which to cut) on a copy stream while the compute
+    stream extracts, projects and normalises the pieces that have arrived (reads
+    are independent).  On one GPU the kNN is incremental as well (knn_overlap,
+    fr_knn_inc_*): after chunk c the new embedding rows are searched against all
+    rows present and the earlier rows against the new ones, so only the last
+    chunk's share of the distance work is left when the copy ends.
+    knn_phase_ends: the chunk counts after which a phase runs.  Default: the last two cuts and the
+    end -- every launch of the distance kernel costs ~0.1 ms of ramp and tail and the rows of a new
+    chunk start their thresholds from -inf on all CTAs at once, so early, small phases cost more
+    than they hide (scripts/e2e_tune.py: 9.3 ms without overlap, 8.8 ms with this schedule, 10.8 ms
+    with a phase after each of 8 equal chunks, c2 on one B200).
+    async_extract: chunks go through fr_extract_async (room for one hit per 8 bases, no host
+    synchronisation per chunk: the host queues the whole step and the GPU is only ever waiting for
+    PCIe); a chunk that does not fit is reported at the end and the step is redone synchronously.
+    direct_out: the re-rank kernel writes the neighbour lists straight into the pinned host buffers
+    (posted PCIe writes while it runs) instead of a device-to-host copy after it; the result's
+    nbr_idx / nbr_dist are then those host tensors."""
     dev = torch.device("cuda", eng.device)
     n = hb.bases.numel()
     R = hb.offsets.numel() - 1
     cur = torch.cuda.current_stream()
+
+    def mark(label, stream=None):           # trace: (label, event) pairs for a timeline of the step
+        if trace is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream or cur)
+            trace.append((label, ev))
+    mark("start")
     copy_stream = _copy_stream(dev)
     bases_d = torch.empty(n + 16, dtype=torch.uint8, device=dev)[:n]
     offsets_d = hb.offsets.to(dev, non_blocking=True)
-    chunks = max(1, min(chunks, R))
-    # read ranges balanced by bases
+    # read ranges by bases: `chunks` equal pieces, or the cumulative fractions given
+    chunks_arg = chunks
+    fracs = [c / chunks for c in range(1, chunks)] if isinstance(chunks, int) else [float(f) for f in chunks if 0 < f < 1]
+    fracs = fracs[: max(0, R - 1)]
     off = hb.offsets
     bounds = [0]
-    for c in range(1, chunks):
-        target = int(off[0]) + (n * c) // chunks
+    for f in fracs:
+        target = int(off[0]) + int(n * f)
         bounds.append(max(bounds[-1], int(torch.searchsorted(off, torch.tensor(target)).item())))
     bounds.append(R)
+    chunks = len(bounds) - 1
     copy_stream.wait_stream(cur)
     events = []
     with torch.cuda.stream(copy_stream):
@@ -145,34 +172,105 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
             ev = torch.cuda.Event()
             ev.record(copy_stream)
             events.append(ev)
+            mark("h2d %d" % c, copy_stream)
     D = P_dev[3]
     E = torch.empty((2 * R, D), dtype=torch.float32, device=dev)
+    multi = group is not None and torch.distributed.get_world_size(group) > 1
+    k_eff = min(k_nn, 2 * R)
+    inc = knn_overlap and mode == 0 and not multi and chunks > 1 and Engine.knn_inc_supported(2 * R, D, k_eff)
+    if inc:
+        default_ends = range(max(1, chunks - 2), chunks + 1)
+        ends = sorted(set(int(e) for e in (knn_phase_ends or default_ends) if 1 <= int(e) < chunks) | {chunks})
+        ends = ends[-64:]                       # fr_knn_inc_begin takes at most 64 phases
+        Dp = (D + 63) // 64 * 64
+        En = torch.empty((2 * R, D), dtype=torch.float32, device=dev)
+        Eh = torch.empty((2 * R, Dp), dtype=torch.float16, device=dev)
+        norms = torch.empty(2 * R, dtype=torch.float32, device=dev)
+        eng.knn_inc_begin(En, Eh, norms, k_eff, [0] + [2 * bounds[e] for e in ends])
+        phase = 0
     ips, ixs, base = [], [], 0
+    status = torch.zeros(2 * chunks, dtype=torch.int64, device=dev) if async_extract else None
     for c in range(chunks):
         r0, r1 = bounds[c], bounds[c + 1]
         cur.wait_event(events[c])
-        if r1 == r0:
-            continue
-        ip, ix = eng.extract(bases_d, offsets_d[r0:r1 + 1])
-        eng.project(ip, ix, P_dev, nk, out=E[2 * r0:2 * r1])
-        ips.append(ip[1:] + base if ips else ip)
-        ixs.append(ix)
-        base += int(ix.numel())
+        if r1 > r0:
+            if async_extract:
+                room = (int(off[r1]) - int(off[r0])) // 8 + (r1 - r0) + 1024
+                ix = torch.empty(room, dtype=torch.int32, device=dev)
+                ip = eng.extract_async(bases_d, offsets_d[r0:r1 + 1], ix, status[2 * c:2 * c + 2])
+                ips.append(ip)
+                ixs.append(ix)
+            else:
+                ip, ix = eng.extract(bases_d, offsets_d[r0:r1 + 1])
+                ips.append(ip[1:] + base if ips else ip)
+                ixs.append(ix)
+                base += int(ix.numel())
+            mark("extract %d" % c)
+            eng.project(ip, ix, P_dev, nk, out=E[2 * r0:2 * r1])
+            mark("project %d" % c)
+            if inc:
+                eng.normalize(E[2 * r0:2 * r1], out=(En[2 * r0:2 * r1], Eh[2 * r0:2 * r1], norms[2 * r0:2 * r1]))
+        if inc and c + 1 == ends[phase]:
+            eng.knn_inc_phase(phase)
+            mark("knn phase %d" % phase)
+            phase += 1
     bases_d.record_stream(copy_stream)
-    indptr = torch.cat(ips) if ips else torch.zeros(1, dtype=torch.int64, device=dev)
-    indices = torch.cat(ixs) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
-    En, Eh, norms = eng.normalize(E)
-    q0, nq, ready = 0, En.shape[0], []
-    if group is not None and torch.distributed.get_world_size(group) > 1:
-        from .parallel import all_gather_rows
-        En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
-    k_eff = min(k_nn, En.shape[0])
-    idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None)
-    res = HotPathResult(indptr, indices, E, idx, dist, q0)
-    hb.nbr_idx[:, : res.nbr_idx.shape[1]].copy_(res.nbr_idx, non_blocking=True)
-    hb.nbr_dist[:, : res.nbr_dist.shape[1]].copy_(res.nbr_dist, non_blocking=True)
-    torch.cuda.current_stream().synchronize()
-    return res
+    if not async_extract:
+        indptr = torch.cat(ips) if ips else torch.zeros(1, dtype=torch.int64, device=dev)
+        indices = torch.cat(ixs) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
+    direct = direct_out and hb.nbr_idx.shape[1] == k_eff and hb.nbr_idx.is_pinned() and hb.nbr_dist.is_pinned()
+    out = (hb.nbr_idx, hb.nbr_dist) if direct else None
+    if inc:
+        idx, dist = eng.knn_inc_finish(out=out)
+        q0 = 0
+    else:
+        En, Eh, norms = eng.normalize(E)
+        q0, nq, ready = 0, En.shape[0], []
+        if multi:
+            from .parallel import all_gather_rows
+            En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
+        if direct and (En.shape[0] < k_nn or nq != hb.nbr_idx.shape[0]):
+            direct, out = False, None
+        k_eff = min(k_nn, En.shape[0])
+        idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None,
+                            out=out)
+    mark("knn done")
+    if not direct:
+        hb.nbr_idx[:, : idx.shape[1]].copy_(idx, non_blocking=True)
+        hb.nbr_dist[:, : dist.shape[1]].copy_(dist, non_blocking=True)
+        mark("d2h")
+    if async_extract:
+        st_h = _pinned_i64(dev, 2 * chunks)
+        st_h.copy_(status, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        st = st_h.tolist()
+        if any(st[0::2]):           # a chunk had more hits than room: redo the step the synchronous way
+            if inc:
+                eng.knn_fallback_rows   # (drains the engine's pending counter read)
+            return run_hot_path_host(eng, hb, P_dev, nk, k_nn, mode=mode, group=group, timers=timers, chunks=chunks_arg,
+                                     rows_per_rank=rows_per_rank, knn_overlap=knn_overlap,
+                                     knn_phase_ends=knn_phase_ends, async_extract=False, direct_out=direct_out)
+        # CSR of the whole read set from the chunks' rows (queued; the neighbour lists have landed)
+        nz = [st[2 * c + 1] for c in range(chunks) if bounds[c + 1] > bounds[c]]
+        parts, base = [], 0
+        for ip, n_c in zip(ips, nz):
+            parts.append(ip[1:] + base if parts else ip)
+            base += n_c
+        indptr = torch.cat(parts) if parts else torch.zeros(1, dtype=torch.int64, device=dev)
+        indices = torch.cat([ix[:n_c] for ix, n_c in zip(ixs, nz)]) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
+    else:
+        torch.cuda.current_stream().synchronize()
+    return HotPathResult(indptr, indices, E, idx, dist, q0)
+
+
+_pinned: dict = {}
+
+
+def _pinned_i64(dev, n: int) -> torch.Tensor:
+    t = _pinned.get((dev.index, n))
+    if t is None:
+        t = _pinned[(dev.index, n)] = torch.empty(n, dtype=torch.int64, pin_memory=True)
+    return t
 
 
 _copy_streams: dict = {}

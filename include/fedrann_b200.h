@@ -95,6 +95,14 @@ int fr_extract_count(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const
 /* Writes the column indices (i32[nnz], ascending inside each row, rows in
  * input order) of the preceding fr_extract_count. */
 int fr_extract_fill(fr_ctx *ctx, int32_t *d_indices, void *stream);
+/* The same in ONE call that never synchronises (for callers that pipeline chunks of reads, e.g.
+ * while later reads still cross PCIe): d_indices has room for `cap` entries; d_status is a device
+ * i64[2] the caller zeroed before the first call.  On completion status[1] = number of non-zeros
+ * and status[0] |= 1/2 (internal scratch too small) | 4 (more than cap non-zeros); when a bit is
+ * set nothing was written and the caller repeats the chunk with fr_extract_count/fill. */
+int fr_extract_async(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, const int64_t *d_offsets,
+                     int64_t n_reads, int64_t *d_indptr, int32_t *d_indices, int64_t cap,
+                     int64_t *d_status, void *stream);
 
 /* ---- K4: E = A.P (feature_extraction.py:204-213, 136-140) ---- */
 /* P in CSR (F = 2*nk rows, D columns): d_p_indptr i64[F+1], d_p_indices
@@ -124,6 +132,20 @@ int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norm
  * tensor-core pass reads only the fp16 copy and starts at once; the first consumer of d_En
  * waits for the event on fr_knn's stream.  One-shot: applies to the next fr_knn call only. */
 int fr_knn_rows_ready_after(fr_ctx *ctx, void *event);
+/* Incremental all-vs-all search (same result as fr_knn mode 0 with q0 = 0, nq = n_db): for callers whose
+ * database rows become available in ranges -- e.g. run_fedrann_pipeline's reads still crossing PCIe
+ * (fedrann/__main__.py:321-365 computes the whole matrix before get_neighbors, nearest_neighbors.py:22).
+ * begin(): d_En / d_Eh / d_norms are the FULL-SIZE arrays ([n_db, D] fp32, [n_db, Dp] fp16, [n_db]); their rows
+ * may still be unwritten.  bounds is a host array of n_phases + 1 cumulative row counts (bounds[0] = 0,
+ * bounds[n_phases] = n_db).  phase(j), j = 0, 1, ... in order: rows [0, bounds[j+1]) of d_Eh and d_norms must
+ * be complete on `stream`; it scores (new rows x all rows present) and (earlier rows x new rows).
+ * finish(): needs every row of d_En; re-ranks, certifies and writes idx / dist [n_db, k].
+ * FR_ERR_ARG from begin() when the shape is outside the tensor-core path (D > 512, k > 128, n_db < 2k):
+ * use fr_knn then. */
+int fr_knn_inc_begin(fr_ctx *ctx, const float *d_En, const void *d_Eh, const float *d_norms, int64_t n_db,
+                     int D, int Dp, int k, int n_phases, const int64_t *bounds, void *stream);
+int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream);
+int fr_knn_inc_finish(fr_ctx *ctx, int32_t *d_idx, float *d_dist, void *stream);
 /* statistics of the last fr_knn call: rows that needed the exact fallback */
 int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
 

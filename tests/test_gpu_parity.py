@@ -252,12 +252,20 @@ def test_host_path_chunked_equals_device_path(eng):
     bases_d, offs_d = eng.dev(rs.bases), eng.dev(rs.offsets)
     a = run_hot_path(eng, bases_d, offs_d, P_dev, lib.nk, knn_k)
     hb = HostBuffers.from_device(bases_d, rs.offsets, 2 * rs.n_reads, knn_k)
-    for chunks in (1, 3, 8, 1000):
-        b = run_hot_path_host(eng, hb, P_dev, lib.nk, knn_k, chunks=chunks)
+    b = run_hot_path_host(eng, hb, P_dev, lib.nk, knn_k)          # the default schedule
+    assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu()) and torch.equal(hb.nbr_dist, a.nbr_dist.cpu())
+    hb.nbr_idx.zero_(); hb.nbr_dist.zero_()
+    for chunks, kw in ((1, {}), (3, {}), (8, dict(knn_phase_ends=range(1, 9))), (1000, {}), (8, dict(knn_overlap=False)),
+                       (40, dict(knn_phase_ends=range(1, 41))),
+                       (8, dict(knn_phase_ends=(3, 6, 7))), (5, dict(async_extract=False)),
+                       (4, dict(async_extract=False, knn_overlap=False)), (8, dict(direct_out=False)),
+                       ((0.3, 0.5, 0.9), {}), (2, dict(knn_overlap=False, direct_out=False))):
+        b = run_hot_path_host(eng, hb, P_dev, lib.nk, knn_k, chunks=chunks, **kw)
         assert torch.equal(a.indptr, b.indptr) and torch.equal(a.indices, b.indices)
         assert torch.equal(a.embedding, b.embedding)
-        assert torch.equal(a.nbr_idx, b.nbr_idx) and torch.equal(a.nbr_dist, b.nbr_dist)
+        assert torch.equal(a.nbr_idx.cpu(), b.nbr_idx.cpu()) and torch.equal(a.nbr_dist.cpu(), b.nbr_dist.cpu())
         assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu()) and torch.equal(hb.nbr_dist, a.nbr_dist.cpu())
+        hb.nbr_idx.zero_(); hb.nbr_dist.zero_()
 
 
 def test_knn_uncertifiable_rows_take_exact_fallback(eng):
@@ -299,3 +307,109 @@ def test_knn_rows_ready_event(eng):
     i2, d2 = eng.knn(late, Eh, norms, 15, mode=1)
     torch.cuda.synchronize()
     assert torch.equal(i1, i_ref) and torch.equal(d1, d_ref) and torch.equal(i2, i_ref)
+
+
+@pytest.mark.parametrize("N,D,k,bounds", [
+    (3000, 100, 10, [0, 1, 130, 130, 1700, 2999, 3000]),          # unaligned, an empty phase, one-row phases
+    (20000, 256, 50, [0, 5000, 10000, 15000, 20000]),
+    (9000, 500, 50, [0, 9000]),                                   # a single phase
+    (7000, 64, 20, [0, 0, 3500, 7000, 7000]),                     # empty first and last phases
+])
+def test_knn_incremental_equals_one_shot(eng, N, D, k, bounds):
+    """fr_knn_inc_*: the database arrives in row ranges; rows that are not there yet hold garbage
+    (NaN) while the earlier phases run.  Same bits as fr_knn on the complete database."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(N + D)
+    X = torch.randn((N, D), device="cuda", generator=g)
+    X[N // 2] = 0.0                                               # a zero-norm row
+    X[7] = X[3]                                                   # exact duplicates (index tie-break)
+    En_full, Eh_full, norms_full = eng.normalize(X)
+    i_ref, d_ref = eng.knn(En_full, Eh_full, norms_full, k, mode=1)
+    En = torch.full_like(En_full, float("nan"))
+    Eh = torch.full_like(Eh_full, float("nan"))
+    norms = torch.full_like(norms_full, float("nan"))
+    eng.knn_inc_begin(En, Eh, norms, k, bounds)
+    for j in range(len(bounds) - 1):
+        a, b = bounds[j], bounds[j + 1]
+        En[a:b], Eh[a:b], norms[a:b] = En_full[a:b], Eh_full[a:b], norms_full[a:b]
+        eng.knn_inc_phase(j)
+    idx, dist = eng.knn_inc_finish()
+    torch.cuda.synchronize()
+    assert torch.equal(idx, i_ref) and torch.equal(dist, d_ref)
+
+
+def test_knn_incremental_argument_errors(eng):
+    from fedrann_b200._lib import FedrannError
+    X = torch.randn((600, 32), device="cuda")
+    En, Eh, norms = eng.normalize(X)
+    with pytest.raises(FedrannError):
+        eng.knn_inc_begin(En, Eh, norms, 10, [0, 300])            # does not reach n_db
+    with pytest.raises(FedrannError):
+        eng.knn_inc_begin(En, Eh, norms, 10, [0, 400, 300, 600])  # decreasing
+    with pytest.raises(FedrannError):
+        eng.knn_inc_begin(En, Eh, norms, 400, [0, 600])           # k outside the tensor-core path
+    eng.knn_inc_begin(En, Eh, norms, 10, [0, 300, 600])
+    with pytest.raises(FedrannError):
+        eng.knn_inc_phase(1)                                      # out of order
+    with pytest.raises(FedrannError):
+        eng.knn_inc_finish()                                      # phases missing
+    eng.knn_inc_phase(0)
+    eng.knn_inc_phase(1)
+    idx, dist = eng.knn_inc_finish()
+    i1, d1 = eng.knn(En, Eh, norms, 10, mode=1)
+    assert torch.equal(idx, i1) and torch.equal(dist, d1)
+    with pytest.raises(FedrannError):
+        eng.knn_inc_phase(0)                                      # nothing in progress
+
+
+def test_extract_async_equals_sync_and_reports_overflow(eng):
+    """fr_extract_async: same CSR as count + fill without a host round trip; a buffer that is too
+    small is reported in the status word and nothing is written."""
+    k = 13
+    g = S.random_genome(30000, 5)
+    rs = S.simulate_reads(g, 10, 5, mean_len=2000, len_model="lognormal", min_len=20, sub=0.02, ins=0.01, dele=0.01,
+                          n_frac=0.003)
+    lib = S.library_from_reads(rs, k, 0.3, 1, 5)
+    eng.build_table(lib.all_codes(), k)
+    b, o = eng.dev(rs.bases), eng.dev(rs.offsets)
+    ip0, ix0 = eng.extract(b, o)
+    nnz = ix0.numel()
+    status = torch.zeros(2, dtype=torch.int64, device="cuda")
+    ix = torch.full((nnz + 100,), -7, dtype=torch.int32, device="cuda")
+    ip = eng.extract_async(b, o, ix, status)
+    torch.cuda.synchronize()
+    assert status.tolist() == [0, nnz]
+    assert torch.equal(ip, ip0) and torch.equal(ix[:nnz], ix0) and bool((ix[nnz:] == -7).all())
+    # exactly enough room, then one entry short
+    ix = torch.full((nnz,), -7, dtype=torch.int32, device="cuda")
+    status.zero_()
+    eng.extract_async(b, o, ix, status)
+    assert status.tolist() == [0, nnz] and torch.equal(ix, ix0)
+    ix = torch.full((nnz - 1,), -7, dtype=torch.int32, device="cuda")
+    status.zero_()
+    eng.extract_async(b, o, ix, status)
+    assert status.tolist() == [4, nnz] and bool((ix == -7).all())
+    # the flag is sticky across calls on the same status word
+    eng.extract_async(b, o, torch.empty(nnz, dtype=torch.int32, device="cuda"), status)
+    assert status.tolist()[0] == 4
+
+
+def test_host_path_redoes_chunks_that_overflow(eng):
+    """A dense library (every k-mer sampled: about one hit per base) does not fit the room the
+    asynchronous chunks get; the step is redone synchronously and the result is the same."""
+    from fedrann_b200.pipeline import HostBuffers, run_hot_path, run_hot_path_host
+    from fedrann_b200.precompute import precompute_matrix
+    k, D, knn_k = 11, 32, 5
+    g = S.random_genome(20000, 8)
+    rs = S.simulate_reads(g, 8, 8, mean_len=1500, len_model="lognormal", min_len=50, sub=0.01, ins=0.0, dele=0.0)
+    lib = S.library_from_reads(rs, k, 1.0, 1, 8)
+    eng.build_table(lib.all_codes(), k)
+    P_dev = eng.upload_projection(precompute_matrix(D, lib.counts, lib.n_features))
+    bases_d, offs_d = eng.dev(rs.bases), eng.dev(rs.offsets)
+    a = run_hot_path(eng, bases_d, offs_d, P_dev, lib.nk, knn_k)
+    assert a.indices.numel() > rs.bases.size // 4
+    hb = HostBuffers.from_device(bases_d, rs.offsets, 2 * rs.n_reads, knn_k)
+    b = run_hot_path_host(eng, hb, P_dev, lib.nk, knn_k, chunks=4)
+    assert torch.equal(a.indptr, b.indptr) and torch.equal(a.indices, b.indices)
+    assert torch.equal(a.nbr_idx.cpu(), b.nbr_idx.cpu()) and torch.equal(a.nbr_dist.cpu(), b.nbr_dist.cpu())
+    assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu())
