@@ -5,9 +5,11 @@
 // replacement executable and the Python host share one implementation.
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_set>
+#include <thread>
 #include <vector>
 
 #include "../../include/fedrann_b200.h"
@@ -54,20 +56,25 @@ extern "C" int fr_library_parse(const char *text, int64_t text_len, int k, uint6
     return FR_OK;
 }
 
-extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64_t *offsets_out,
-                              char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len) {
-    if (!text || text_len < 0 || !n_reads || !n_bases || !names_len) return FR_ERR_ARG;
-    const bool emit = bases_out != nullptr;
-    int64_t R = 0, B = 0, NL = 0;
-    bool checked = false, is_fastq = false;
+namespace {
+
+struct FastxCount { int64_t R = 0, B = 0, NL = 0; };
+
+// The record state machine of read_sequences (kmer_searcher.cpp:153-201) over text[beg, end).
+// For FASTA a range that starts at a header line is independent of what precedes it, so large
+// inputs are parsed by several threads (ranges cut at "\n>"); with emit set the outputs are
+// written at the given record / base / name offsets.
+FastxCount fastx_range(const char *text, int64_t beg, int64_t end, bool is_fastq, bool emit, uint8_t *bases_out,
+                       int64_t *offsets_out, char *names_out, FastxCount at) {
+    int64_t R = at.R, B = at.B, NL = at.NL;
     bool have_rec = false;  // FASTA: a record with a non-empty id is open
-    int64_t pos = 0;
+    int64_t pos = beg;
     auto next_line = [&](int64_t &ls, int64_t &le) -> bool {
-        if (pos >= text_len) return false;
+        if (pos >= end) return false;
         ls = pos;
-        const void *nl = memchr(text + pos, '\n', (size_t)(text_len - pos));
-        le = nl ? (const char *)nl - text : text_len;
-        pos = nl ? le + 1 : text_len;
+        const void *nl = memchr(text + pos, '\n', (size_t)(end - pos));
+        le = nl ? (const char *)nl - text : end;
+        pos = nl ? le + 1 : end;
         return true;
     };
     auto open_rec = [&](const char *id, int64_t idlen) {
@@ -79,9 +86,7 @@ extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases
         NL += idlen + 1;
     };
     int64_t ls, le;
-    if (emit) offsets_out[0] = 0;
     while (next_line(ls, le)) {
-        if (!checked) { is_fastq = le > ls && text[ls] == '@'; checked = true; }   // :163-166
         if (le == ls) continue;                                                     // :168
         if (!is_fastq) {
             if (text[ls] == '>') {
@@ -107,8 +112,65 @@ extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases
         }
     }
     if (!is_fastq && have_rec) ++R;
-    if (emit) offsets_out[R] = B;
-    *n_reads = R; *n_bases = B; *names_len = NL;
+    FastxCount out;
+    out.R = R - at.R; out.B = B - at.B; out.NL = NL - at.NL;
+    return out;
+}
+
+}  // namespace
+
+extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64_t *offsets_out,
+                              char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len) {
+    if (!text || text_len < 0 || !n_reads || !n_bases || !names_len) return FR_ERR_ARG;
+    const bool emit = bases_out != nullptr;
+    // the format is decided by the first line (:163-166)
+    const bool is_fastq = text_len > 0 && text[0] == '@';
+    // FASTA ranges: cut at header lines, one range per thread (FR_PARSE_THREADS / FR_PARSE_MIN_RANGE: tests)
+    int64_t min_range = 8 << 20;
+    int threads = (int)std::thread::hardware_concurrency();
+    if (threads > 16) threads = 16;
+    if (const char *e = getenv("FR_PARSE_THREADS")) threads = atoi(e);
+    if (const char *e = getenv("FR_PARSE_MIN_RANGE")) min_range = atoll(e);
+    if (min_range < 1) min_range = 1;
+    if (threads < 1 || is_fastq) threads = 1;
+    if ((int64_t)threads > text_len / min_range) threads = (int)(text_len / min_range);
+    if (threads < 1) threads = 1;
+    std::vector<int64_t> cut(1, 0);
+    for (int t = 1; t < threads; ++t) {
+        int64_t p = text_len / threads * t;
+        if (p < cut.back()) p = cut.back();
+        int64_t c = -1;
+        while (p < text_len) {                       // next "\n>"
+            const void *nl = memchr(text + p, '\n', (size_t)(text_len - p));
+            if (!nl) break;
+            p = (const char *)nl - text + 1;
+            if (p < text_len && text[p] == '>') { c = p; break; }
+        }
+        if (c < 0) break;
+        if (c > cut.back()) cut.push_back(c);
+    }
+    cut.push_back(text_len);
+    const int nr = (int)cut.size() - 1;
+    std::vector<FastxCount> cnt(nr), at(nr + 1);
+    auto run = [&](bool do_emit) {
+        std::vector<std::thread> th;
+        for (int t = 1; t < nr; ++t)
+            th.emplace_back([&, t] {
+                cnt[t] = fastx_range(text, cut[t], cut[t + 1], is_fastq, do_emit, bases_out, offsets_out, names_out, at[t]);
+            });
+        cnt[0] = fastx_range(text, cut[0], cut[1], is_fastq, do_emit, bases_out, offsets_out, names_out, at[0]);
+        for (auto &x : th) x.join();
+    };
+    run(false);
+    for (int t = 0; t < nr; ++t) {
+        at[t + 1].R = at[t].R + cnt[t].R; at[t + 1].B = at[t].B + cnt[t].B; at[t + 1].NL = at[t].NL + cnt[t].NL;
+    }
+    if (emit) {
+        run(true);
+        offsets_out[0] = 0;
+        offsets_out[at[nr].R] = at[nr].B;
+    }
+    *n_reads = at[nr].R; *n_bases = at[nr].B; *names_len = at[nr].NL;
     return FR_OK;
 }
 

@@ -94,3 +94,39 @@ def test_output_bin_roundtrip(tmp_path):
     f = str(tmp_path / "kmer_frequency.bin")
     engine.write_frequency_bin(f, np.array([0, 2, 0, 7], dtype=np.uint32))
     assert O.read_frequency_bin(f) == {1: 2, 3: 7}
+
+
+def _tricky_fasta(nrec, seed):
+    r = np.random.default_rng(seed)
+    parts = [b"junk before the first header\n\n"]
+    alphabet = np.frombuffer(b"ACGTNacgt>@", dtype=np.uint8)
+    for i in range(nrec):
+        kind = r.integers(0, 10)
+        parts.append(b">\n" if kind == 0 else (b">r%d\tdesc > x\n" % i if kind == 1 else b">r%d some desc\n" % i))
+        for _ in range(r.integers(0, 4)):
+            line = bytes(r.choice(alphabet, size=int(r.integers(0, 50))))
+            if line.startswith(b">"):
+                line = b"A" + line
+            parts.append(line + (b"\r\n" if r.integers(0, 8) == 0 else b"\n"))
+        if r.integers(0, 5) == 0:
+            parts.append(b"\n")
+    return b"".join(parts)
+
+
+@pytest.mark.parametrize("threads,min_range", [(1, 1 << 30), (7, 64), (16, 1), (3, 1000)])
+def test_fasta_parse_in_parallel_ranges_equals_oracle(monkeypatch, threads, min_range):
+    """Large FASTA inputs are parsed by several threads over ranges cut at header lines
+    (FR_PARSE_THREADS / FR_PARSE_MIN_RANGE shrink the ranges so that small inputs take that path)."""
+    from fedrann_b200 import engine
+    monkeypatch.setenv("FR_PARSE_THREADS", str(threads))
+    monkeypatch.setenv("FR_PARSE_MIN_RANGE", str(min_range))
+    for seed in range(4):
+        text = _tricky_fasta(300, seed)
+        b2, o2, n2 = reads_to_arrays(O.parse_fastx(text))
+        b, o, n = engine.parse_fastx(text)
+        assert n == n2 and np.array_equal(o, o2) and b.tobytes() == b2.tobytes()
+    # FASTQ stays on one thread ('@' may start a quality line)
+    fq = b"".join(b"@q%d\nACGT\n+\n@@@@\n" % i for i in range(200))
+    b2, o2, n2 = reads_to_arrays(O.parse_fastx(fq))
+    b, o, n = engine.parse_fastx(fq)
+    assert n == n2 and np.array_equal(o, o2) and b.tobytes() == b2.tobytes()
