@@ -167,7 +167,9 @@ int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, in
 // query (their rows sit in shared memory) and stores orderable 64-bit keys (distance, index);
 // then one CTA per query finds its k smallest keys exactly -- a bitwise binary search for the
 // k-th smallest key over the whole key array, a gather of the k keys at or below it, a sort.
-#define FR_FB_MAX 32        // queries answered per launch (the rest take the scan above)
+#define FR_FB_MAX 32        // queries answered per launch
+#define FR_FB_BATCHES 4     // launches queued unconditionally (each returns at once when there is nothing
+                            // left for it); rows beyond FR_FB_BATCHES * FR_FB_MAX take the scan above
 #define FR_FB_QB 8          // queries per block of the distance kernel
 
 __device__ __forceinline__ uint32_t fr_f2ord(float f) {
@@ -180,14 +182,15 @@ __device__ __forceinline__ float fr_ord2f(uint32_t u) {
 
 __global__ void __launch_bounds__(256)
 fr_knn_fb_dist_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
-                      const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int fb_max,
-                      unsigned long long *__restrict__ keys) {
+                      const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int f_base,
+                      int fb_max, unsigned long long *__restrict__ keys) {
     extern __shared__ __align__(16) unsigned char fr_fb_smem[];
     float *qbuf = reinterpret_cast<float *>(fr_fb_smem);          // [FR_FB_QB][D]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t total = min((int64_t)(*n_rows), (int64_t)fb_max);
+    const int64_t total = min((int64_t)(*n_rows) - f_base, (int64_t)fb_max);   // rows of this batch
     const int f0 = blockIdx.y * FR_FB_QB;
     if (f0 >= total) return;
+    rows += f_base;
     const int nf = (int)min((int64_t)FR_FB_QB, total - f0);
     float qn[FR_FB_QB];
     for (int u = 0; u < nf; ++u) {
@@ -224,14 +227,15 @@ fr_knn_fb_dist_kernel(const float *__restrict__ En, const float *__restrict__ no
 
 __global__ void __launch_bounds__(1024)
 fr_knn_fb_select_kernel(const unsigned long long *__restrict__ keys, int64_t n_db, int k,
-                        const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int fb_max,
-                        int32_t *__restrict__ out_idx, float *__restrict__ out_dist) {
+                        const int32_t *__restrict__ rows, const unsigned long long *__restrict__ n_rows, int f_base,
+                        int fb_max, int32_t *__restrict__ out_idx, float *__restrict__ out_dist) {
     __shared__ int s_part[32];
     __shared__ int s_total;
     __shared__ int s_n;
     __shared__ unsigned long long s_keys[FR_MAX_K * 2];
     const int f = blockIdx.x;
-    if (f >= (int)min((int64_t)(*n_rows), (int64_t)fb_max)) return;
+    if (f >= min((int64_t)(*n_rows) - f_base, (int64_t)fb_max)) return;
+    rows += f_base;
     const unsigned long long *kp = keys + (int64_t)f * n_db;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // X = k-th smallest key: the largest x with count(keys < x) <= k - 1
@@ -287,23 +291,25 @@ int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms,
                            float *d_dist, int *rows_covered, cudaStream_t st) {
     *rows_covered = 0;
     if (k < 1 || k > FR_MAX_K || n_db < k) return FR_OK;
-    // scratch: fb_max x n_db keys, at most 256 MB
+    // scratch: fb_max x n_db keys, at most 1 GB
     int fb_max = FR_FB_MAX;
-    while (fb_max > 1 && (int64_t)fb_max * n_db * 8 > (256ll << 20)) fb_max >>= 1;
+    while (fb_max > 1 && (int64_t)fb_max * n_db * 8 > (1ll << 30)) fb_max >>= 1;
     if ((int64_t)fb_max * n_db * 8 > (1ll << 31)) return FR_OK;
     int rc = fr_ensure(ctx, &ctx->d_knn_fb, &ctx->knn_fb_cap, (int64_t)fb_max * n_db * 8, "kNN fallback keys");
     if (rc) return rc;
     const size_t smem = (size_t)FR_FB_QB * D * sizeof(float);
     FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_fb_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)(ctx->sm_count * 4), (unsigned)((fb_max + FR_FB_QB - 1) / FR_FB_QB));
-    fr_kt_begin(ctx, "fr_knn_fb_dist_kernel", st);
-    fr_knn_fb_dist_kernel<<<grid, 256, smem, st>>>(d_En, d_norms, n_db, D, q0, d_rows, d_n_rows, fb_max,
-                                                   (unsigned long long *)ctx->d_knn_fb);
-    FR_LAUNCH_CHECK(ctx, "fr_knn_fb_dist_kernel");
-    fr_kt_begin(ctx, "fr_knn_fb_select_kernel", st);
-    fr_knn_fb_select_kernel<<<fb_max, 1024, 0, st>>>((const unsigned long long *)ctx->d_knn_fb, n_db, k, d_rows,
-                                                     d_n_rows, fb_max, d_idx, d_dist);
-    FR_LAUNCH_CHECK(ctx, "fr_knn_fb_select_kernel");
-    *rows_covered = fb_max;
+    for (int b = 0; b < FR_FB_BATCHES; ++b) {
+        fr_kt_begin(ctx, "fr_knn_fb_dist_kernel", st);
+        fr_knn_fb_dist_kernel<<<grid, 256, smem, st>>>(d_En, d_norms, n_db, D, q0, d_rows, d_n_rows, b * fb_max, fb_max,
+                                                       (unsigned long long *)ctx->d_knn_fb);
+        FR_LAUNCH_CHECK(ctx, "fr_knn_fb_dist_kernel");
+        fr_kt_begin(ctx, "fr_knn_fb_select_kernel", st);
+        fr_knn_fb_select_kernel<<<fb_max, 1024, 0, st>>>((const unsigned long long *)ctx->d_knn_fb, n_db, k, d_rows,
+                                                         d_n_rows, b * fb_max, fb_max, d_idx, d_dist);
+        FR_LAUNCH_CHECK(ctx, "fr_knn_fb_select_kernel");
+    }
+    *rows_covered = FR_FB_BATCHES * fb_max;
     return FR_OK;
 }

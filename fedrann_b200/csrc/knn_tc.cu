@@ -436,6 +436,10 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 mbar_wait_t(bTFull + 8 * ab, (tile >> 1) & 1, w0, dbg_on);
                 tc_fence_after();
                 const float thr = s_thr[row_in_tile];
+                // the row's shared threshold is requested now and looked at after the tile's filter: an
+                // L2 round trip between the two tile barriers would stall both warps of the quadrant
+                unsigned int g_seen = 0;
+                if (sub == 0 && valid) g_seen = __ldcg(p.gthr + wrow);
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
                 const int64_t col0 = p.db0 + t * TC_N;
                 const bool ragged = col0 + TC_N > p.db_end;
@@ -485,8 +489,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 // that CTA keeps >= klo candidates at or above it.  Adopting it spares the CTAs that
                 // joined the row late (several slots per query tile: multi-GPU, small query sets)
                 // the slow climb from -inf.  s_thr only ever rises (it bounds everything dropped).
-                if (sub == 0 && valid) {
-                    const float gt = ord2f(__ldcg(p.gthr + wrow));
+                if (sub == 0 && valid && g_seen) {
+                    const float gt = ord2f(g_seen);
                     if (gt > s_thr[row_in_tile]) s_thr[row_in_tile] = gt;
                 }
                 tc_quad_bar(bar_id);                     // both warps hold the same counts before either rewrites them

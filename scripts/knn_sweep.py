@@ -1,6 +1,7 @@
 """kNN-only sweep (BASELINE.json configs[4]): N unit-normalised standard-normal rows x D, exact cosine kNN.
-    python scripts/knn_sweep.py [N ...]      -> one JSON line per (N, D, k)"""
-import json, sys
+    python scripts/knn_sweep.py [N ...]      -> one JSON line per (N, D, k)
+    (KNN_SWEEP_D / KNN_SWEEP_K: comma-separated subsets)"""
+import json, os, sys
 import torch
 sys.path.insert(0, ".")
 from fedrann_b200.engine import Engine
@@ -22,6 +23,8 @@ def run(eng, N, D, k):
     torch.cuda.synchronize()
     kt = eng.kernel_times()
     eng.profile(False)
+    fb = eng.knn_fallback_rows                     # (the spot check below resets the counter)
+    fb_ms = sum(kt[n][1] for n in ("fr_knn_fb_dist_kernel", "fr_knn_fb_select_kernel", "fr_knn_exact_kernel") if n in kt)
     ms = e0.elapsed_time(e1)
     # spot check against the exact scan on 64 query rows
     q0 = N // 3
@@ -31,7 +34,7 @@ def run(eng, N, D, k):
     k6 = kt["fr_knn_tc_kernel"][1]
     print(json.dumps({"N": N, "D": D, "k": k, "ms": round(ms, 2), "rows_per_s": round(N / ms * 1e3),
                       "k6_ms": round(k6, 2), "k6_tflops": round(2.0 * N * N * D / k6 / 1e9, 1),
-                      "k7_ms": round(kt["fr_knn_rerank_kernel"][1], 2), "fallback_rows": eng.knn_fallback_rows,
+                      "k7_ms": round(kt["fr_knn_rerank_kernel"][1], 2), "fallback_rows": fb, "fallback_ms": round(fb_ms, 2),
                       "bit_equal_exact_scan_64_rows": ok}), flush=True)
     del En, Eh, norms, idx, dist
     torch.cuda.empty_cache()
@@ -41,6 +44,6 @@ if __name__ == "__main__":
     Ns = [int(a) for a in sys.argv[1:]] or [1_000_000]
     eng = Engine(0)
     for N in Ns:
-        for D in (64, 128, 256, 512):
-            for k in (10, 50):
+        for D in [int(x) for x in os.environ.get("KNN_SWEEP_D", "64,128,256,512").split(",")]:
+            for k in [int(x) for x in os.environ.get("KNN_SWEEP_K", "10,50").split(",")]:
                 run(eng, N, D, k)
