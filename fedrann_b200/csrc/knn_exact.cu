@@ -167,9 +167,10 @@ int fr_knn_exact_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, in
 // query (their rows sit in shared memory) and stores orderable 64-bit keys (distance, index);
 // then one CTA per query finds its k smallest keys exactly -- a bitwise binary search for the
 // k-th smallest key over the whole key array, a gather of the k keys at or below it, a sort.
-#define FR_FB_MAX 32        // queries answered per launch
-#define FR_FB_BATCHES 4     // launches queued unconditionally (each returns at once when there is nothing
-                            // left for it); rows beyond FR_FB_BATCHES * FR_FB_MAX take the scan above
+#define FR_FB_MAX 128       // queries answered per launch pair (fewer when n_db is large: <= 1 GB of keys).
+                            // Large databases get several launch pairs (each returns at once when nothing is
+                            // left for it): there one warp scanning the whole database per query is far too
+                            // slow for a handful of rows.  The rest take the scan above.
 #define FR_FB_QB 8          // queries per block of the distance kernel
 
 __device__ __forceinline__ uint32_t fr_f2ord(float f) {
@@ -293,14 +294,16 @@ int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms,
     if (k < 1 || k > FR_MAX_K || n_db < k) return FR_OK;
     // scratch: fb_max x n_db keys, at most 1 GB
     int fb_max = FR_FB_MAX;
-    while (fb_max > 1 && (int64_t)fb_max * n_db * 8 > (1ll << 30)) fb_max >>= 1;
+    while (fb_max > 8 && (int64_t)fb_max * n_db * 8 > (1ll << 30)) fb_max >>= 1;
     if ((int64_t)fb_max * n_db * 8 > (1ll << 31)) return FR_OK;
     int rc = fr_ensure(ctx, &ctx->d_knn_fb, &ctx->knn_fb_cap, (int64_t)fb_max * n_db * 8, "kNN fallback keys");
     if (rc) return rc;
     const size_t smem = (size_t)FR_FB_QB * D * sizeof(float);
     FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_fb_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)(ctx->sm_count * 4), (unsigned)((fb_max + FR_FB_QB - 1) / FR_FB_QB));
-    for (int b = 0; b < FR_FB_BATCHES; ++b) {
+    int batches = (int)(n_db / 250000);
+    batches = batches < 1 ? 1 : (batches > 64 ? 64 : batches);
+    for (int b = 0; b < batches; ++b) {
         fr_kt_begin(ctx, "fr_knn_fb_dist_kernel", st);
         fr_knn_fb_dist_kernel<<<grid, 256, smem, st>>>(d_En, d_norms, n_db, D, q0, d_rows, d_n_rows, b * fb_max, fb_max,
                                                        (unsigned long long *)ctx->d_knn_fb);
@@ -310,6 +313,6 @@ int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms,
                                                          d_n_rows, b * fb_max, fb_max, d_idx, d_dist);
         FR_LAUNCH_CHECK(ctx, "fr_knn_fb_select_kernel");
     }
-    *rows_covered = FR_FB_BATCHES * fb_max;
+    *rows_covered = batches * fb_max;
     return FR_OK;
 }

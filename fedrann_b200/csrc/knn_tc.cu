@@ -623,6 +623,47 @@ __device__ int rr_compact(unsigned long long *cand, int n, uint32_t Lo) {
     return m;
 }
 
+// Merge of a row whose buffers hold more keys than the merge area (a row with many buffers: incremental
+// search).  Keys below G - 2 eps are dropped while merging (G = the row's shared threshold: one buffer
+// holds > k candidates at or above it, so the k-th best score is >= G and such a key can neither be a
+// survivor nor move T); if the area still fills up the same argument is applied to the k-th best score
+// merged so far.  Returns the number of keys in cand, -1 when they do not fit; *tau as in the caller.
+__device__ __noinline__ int rr_merge_filtered(unsigned long long *cand, int max_n, int64_t row, int slots, int cap,
+                                              const unsigned long long *__restrict__ keys,
+                                              const int *__restrict__ counts, const float *__restrict__ thrs,
+                                              unsigned int g, int k, float *tau_out) {
+    const int lane = threadIdx.x & 31;
+    uint32_t Lg = g ? f2ord(ord2f(g) - 2.0f * TC_EPS) : 0u;
+    float tau = *tau_out;
+    int n = 0;
+    for (int s = 0; s < slots; ++s) {
+        const int cc = counts[row * slots + s];
+        const int c0 = cc & 0xFFFF, c = c0 + (cc >> 16);      // front part, total (rest sits at the end)
+        if (c == 0) continue;
+        tau = fmaxf(tau, thrs[row * slots + s]);
+        const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
+        for (int i0 = 0; i0 < c; i0 += 32) {
+            const int i = i0 + lane;
+            const unsigned long long key = i < c ? __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0))) : 0ull;
+            bool kp = i < c && (uint32_t)(key >> 32) >= Lg;
+            unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
+            if (n + __popc(bal) > max_n && n >= k) {
+                __syncwarp();
+                const uint32_t lo2 = f2ord(ord2f(rr_kth(cand, n, k)) - 2.0f * TC_EPS);
+                if (lo2 > Lg) { Lg = lo2; n = rr_compact(cand, n, Lg); }
+                kp = i < c && (uint32_t)(key >> 32) >= Lg;
+                bal = __ballot_sync(0xFFFFFFFFu, kp);
+            }
+            const int add = __popc(bal);
+            if (n + add > max_n) { *tau_out = tau; return -1; }
+            if (kp) cand[n + __popc(bal & ((1u << lane) - 1))] = key;
+            n += add;
+        }
+    }
+    *tau_out = tau;
+    return n;
+}
+
 __global__ void __launch_bounds__(RR_WARPS * 32)
 fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ norms, int64_t n_db, int D, int64_t q0,
                      int64_t nq, int k, int slots, int cap, int max_n, const unsigned long long *__restrict__ keys,
@@ -644,17 +685,10 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
         int n = 0;
         float tau = -INFINITY;      // largest final threshold of a buffer that ever dropped something
         bool ok = true;
-        // One of the row's buffers holds >= klo (> k) candidates at or above the shared threshold G
-        // (K6 raises it only after such a selection), so the k-th best score is >= G and a candidate
-        // below G - 2 eps can neither be a survivor nor move T: it is dropped while merging.
-        // When the merge area fills up (a row with many buffers: incremental search) the same argument
-        // is applied to the k-th best score merged so far.
-        // Rows whose buffers fit as they are (the usual case of a one-shot search) are copied plainly.
+        // rows whose buffers fit the merge area as they are (the usual case) are copied plainly
         int total = 0;
         for (int s = lane; s < slots; s += 32) { const int cc = counts[row * slots + s]; total += (cc & 0xFFFF) + (cc >> 16); }
         total = __reduce_add_sync(0xFFFFFFFFu, total);
-        const unsigned int g = total > max_n ? gthr[row] : 0u;
-        uint32_t Lg = g ? f2ord(ord2f(g) - 2.0f * TC_EPS) : 0u;
         if (total <= max_n) {
             for (int s = 0; s < slots; ++s) {
                 const int cc = counts[row * slots + s];
@@ -665,30 +699,9 @@ fr_knn_rerank_kernel(const float *__restrict__ En, const float *__restrict__ nor
                 for (int i = lane; i < c; i += 32) cand[n + i] = __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0)));
                 n += c;
             }
-        } else
-        for (int s = 0; s < slots && ok; ++s) {
-            const int cc = counts[row * slots + s];
-            const int c0 = cc & 0xFFFF, c = c0 + (cc >> 16);      // front part, total (rest sits at the end)
-            if (c == 0) continue;
-            tau = fmaxf(tau, thrs[row * slots + s]);
-            const unsigned long long *src = keys + (row * slots + s) * (int64_t)cap;
-            for (int i0 = 0; i0 < c; i0 += 32) {
-                const int i = i0 + lane;
-                const unsigned long long key = i < c ? __ldcg(src + (i < c0 ? i : cap - 1 - (i - c0))) : 0ull;
-                bool kp = i < c && (uint32_t)(key >> 32) >= Lg;
-                unsigned bal = __ballot_sync(0xFFFFFFFFu, kp);
-                if (n + __popc(bal) > max_n && n >= k) {
-                    __syncwarp();
-                    const uint32_t lo2 = f2ord(ord2f(rr_kth(cand, n, k)) - 2.0f * TC_EPS);
-                    if (lo2 > Lg) { Lg = lo2; n = rr_compact(cand, n, Lg); }
-                    kp = i < c && (uint32_t)(key >> 32) >= Lg;
-                    bal = __ballot_sync(0xFFFFFFFFu, kp);
-                }
-                const int add = __popc(bal);
-                if (n + add > max_n) { ok = false; break; }
-                if (kp) cand[n + __popc(bal & ((1u << lane) - 1))] = key;
-                n += add;
-            }
+        } else {
+            n = rr_merge_filtered(cand, max_n, row, slots, cap, keys, counts, thrs, gthr[row], k, &tau);
+            if (n < 0) { ok = false; n = 0; }
         }
         __syncwarp();
         ok = ok && n >= k;
