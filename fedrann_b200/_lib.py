@@ -18,7 +18,7 @@ _ERR = {-1: "FR_ERR_CUDA", -2: "FR_ERR_ARG", -3: "FR_ERR_STATE", -4: "FR_ERR_NOM
 SYMBOLS = [
     "fr_version", "fr_create", "fr_destroy", "fr_last_error", "fr_launch_count",
     "fr_profile_enable", "fr_profile_read",
-    "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin",
+    "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin", "fr_read_output_bin",
     "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_extract_async", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_rows_ready_after", "fr_knn_last_fallback_rows",
     "fr_knn_inc_begin", "fr_knn_inc_phase", "fr_knn_inc_finish",
@@ -67,6 +67,8 @@ def lib():
     L.fr_fastx_parse.argtypes = [C.c_char_p, i64, vp, vp, vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
     L.fr_write_output_bin.argtypes = [C.c_char_p, vp, vp, i64, vp, vp]
     L.fr_write_frequency_bin.argtypes = [C.c_char_p, vp, i64]
+    L.fr_read_output_bin.argtypes = [vp, i64, vp, vp, vp, vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64),
+                                     C.POINTER(i32)]
     L.fr_table_build.argtypes = [vp, vp, i64, i32, vp]
     L.fr_extract_count.argtypes = [vp, vp, i64, vp, i64, vp, vp, C.POINTER(i64), vp]
     L.fr_extract_fill.argtypes = [vp, vp, vp]

@@ -210,6 +210,47 @@ extern "C" int fr_write_output_bin(const char *path, const char *names, const in
     return rc;
 }
 
+// feature_extraction.py:108-132, the reader of output.bin: one sequential pass (records are variable-length).
+// Two-call protocol like fr_fastx_parse: with indptr_out == NULL only the sizes are returned.  status_out:
+// 0 ok, 1 header shorter than 16 bytes, 2 wrong magic, 3 wrong version (returned in *n_records), 4 truncated record.
+extern "C" int fr_read_output_bin(const unsigned char *blob, int64_t len, char *names_out, int64_t *name_offsets_out,
+                                  int64_t *indptr_out, int64_t *indices_out, int64_t *n_records, int64_t *nnz,
+                                  int64_t *names_len, int *status_out) {
+    if (!blob || len < 0 || !n_records || !nnz || !names_len || !status_out) return FR_ERR_ARG;
+    *status_out = 0; *n_records = 0; *nnz = 0; *names_len = 0;
+    if (len < 16) { *status_out = 1; return FR_OK; }
+    if (memcmp(blob, "KMER", 4) != 0) { *status_out = 2; return FR_OK; }
+    if (blob[4] != 1) { *status_out = 3; *n_records = blob[4]; return FR_OK; }
+    uint64_t total;
+    memcpy(&total, blob + 8, 8);
+    const bool emit = indptr_out != nullptr;
+    int64_t pos = 16, nz = 0, nl = 0;
+    if (emit) { indptr_out[0] = 0; name_offsets_out[0] = 0; }
+    for (uint64_t r = 0; r < total; ++r) {
+        if (pos + 2 > len) { *status_out = 4; return FR_OK; }
+        uint16_t idlen;
+        memcpy(&idlen, blob + pos, 2);
+        pos += 2;
+        if (pos + (int64_t)idlen + 4 > len) { *status_out = 4; return FR_OK; }
+        if (emit) memcpy(names_out + nl, blob + pos, idlen);
+        nl += idlen;
+        pos += idlen;
+        uint32_t cnt;
+        memcpy(&cnt, blob + pos, 4);
+        pos += 4;
+        if (pos + 8 * (int64_t)cnt > len) { *status_out = 4; return FR_OK; }
+        if (emit) {
+            memcpy(indices_out + nz, blob + pos, 8 * (size_t)cnt);      // little-endian u64, as stored
+            indptr_out[r + 1] = nz + cnt;
+            name_offsets_out[r + 1] = nl;
+        }
+        nz += cnt;
+        pos += 8 * (int64_t)cnt;
+    }
+    *n_records = (int64_t)total; *nnz = nz; *names_len = nl;
+    return FR_OK;
+}
+
 extern "C" int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features) {
     FILE *f = fopen(path, "wb");
     if (!f) return FR_ERR_ARG;

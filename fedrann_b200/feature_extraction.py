@@ -17,39 +17,47 @@ from .custom_logging import logger
 
 
 def read_output_bin(ks_file: str):
-    """output.bin (kmer_searcher.cpp:98-130) -> (names, indptr int64[R+1], indices int64[nnz])."""
-    with open(ks_file, "rb") as f:
-        blob = f.read()
-    if len(blob) < 16:
-        raise ValueError("文件头不完整")
-    if blob[:4] != b"KMER":
-        raise ValueError("无效的文件格式")
-    if blob[4] != 1:
-        raise ValueError(f"不支持的版本号: {blob[4]}")
-    total = int(np.frombuffer(blob, dtype="<u8", count=1, offset=8)[0])
-    names, counts, starts = [], np.zeros(total, dtype=np.int64), np.zeros(total, dtype=np.int64)
-    pos = 16
-    mv = memoryview(blob)
-    for r in range(total):
-        id_len = mv[pos] | (mv[pos + 1] << 8)
-        pos += 2
-        raw = bytes(mv[pos:pos + id_len])
-        try:
-            names.append(raw.decode("utf-8"))
-        except UnicodeDecodeError:
-            names.append("".join(chr(b) if b < 128 else "_" for b in raw))
-        pos += id_len
-        n = int.from_bytes(mv[pos:pos + 4], "little")
-        pos += 4
-        counts[r], starts[r] = n, pos
-        pos += 8 * n
-    indptr = np.zeros(total + 1, dtype=np.int64)
-    np.cumsum(counts, out=indptr[1:])
-    indices = np.empty(int(indptr[-1]), dtype=np.int64)
-    buf = np.frombuffer(blob, dtype=np.uint8)
-    for r in range(total):
-        if counts[r]:
-            indices[indptr[r]:indptr[r + 1]] = buf[starts[r]:starts[r] + 8 * counts[r]].view("<u8")
+    """output.bin (kmer_searcher.cpp:98-130) -> (names, indptr int64[R+1], indices int64[nnz]).
+    One native pass over the file image (fr_read_output_bin); the error cases and messages are the
+    reference reader's (feature_extraction.py:109-117)."""
+    import ctypes as C
+    from . import _lib
+    L = _lib.lib()
+    blob = np.fromfile(ks_file, dtype=np.uint8)
+    bp = blob.ctypes.data_as(C.c_void_p)
+    nr, nnz, nl, st = C.c_int64(0), C.c_int64(0), C.c_int64(0), C.c_int(0)
+
+    def call(names, noff, indptr, indices):
+        _lib.check(None, L.fr_read_output_bin(bp, blob.size, names, noff, indptr, indices, C.byref(nr), C.byref(nnz),
+                                              C.byref(nl), C.byref(st)), "fr_read_output_bin")
+        if st.value == 1:
+            raise ValueError("文件头不完整")
+        if st.value == 2:
+            raise ValueError("无效的文件格式")
+        if st.value == 3:
+            raise ValueError(f"不支持的版本号: {nr.value}")
+        if st.value == 4:
+            raise ValueError("output.bin is truncated")       # the reference dies in struct.unpack here
+
+    call(None, None, None, None)
+    name_bytes = np.zeros(max(nl.value, 1), dtype=np.uint8)
+    noff = np.zeros(nr.value + 1, dtype=np.int64)
+    indptr = np.zeros(nr.value + 1, dtype=np.int64)
+    indices = np.empty(nnz.value, dtype=np.int64)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    call(vp(name_bytes), vp(noff), vp(indptr), vp(indices))
+    raw = name_bytes.tobytes()
+    try:                                    # ASCII ids (the writer refuses anything else): one decode, then slices
+        text = raw.decode("ascii")
+        names = [text[noff[r]:noff[r + 1]] for r in range(nr.value)]
+    except UnicodeDecodeError:
+        names = []
+        for r in range(nr.value):
+            b = raw[noff[r]:noff[r + 1]]
+            try:
+                names.append(b.decode("utf-8"))
+            except UnicodeDecodeError:
+                names.append("".join(chr(c) if c < 128 else "_" for c in b))
     return names, indptr, indices
 
 

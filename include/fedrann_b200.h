@@ -70,6 +70,18 @@ int fr_write_output_bin(const char *path, const char *names, const int64_t *name
                         int64_t n_reads, const int64_t *indptr, const int32_t *indices);
 int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features);
 
+/* feature_extraction.py:108-132 (parse_kmer_searcher_output) and :295-302
+ * (get_metadata): output.bin, held in memory, -> names + CSR.  Two-call
+ * protocol: with indptr_out == NULL only n_records / nnz / names_len are
+ * returned.  names_out receives the id bytes back to back, name_offsets_out
+ * [n_records + 1] their bounds; indices keep the file's 64-bit values.
+ * status_out: 0 ok, 1 header incomplete, 2 wrong magic, 3 unsupported version
+ * (the version is returned in n_records), 4 truncated record -- the cases
+ * the reference raises on. */
+int fr_read_output_bin(const unsigned char *blob, int64_t len, char *names_out,
+                       int64_t *name_offsets_out, int64_t *indptr_out, int64_t *indices_out,
+                       int64_t *n_records, int64_t *nnz, int64_t *names_len, int *status_out);
+
 /* ---- K2: k-mer library -> device lookup table (kmer_searcher.cpp:259-273) ---- */
 /* d_codes: device u64[n], feature index -> k-mer code, all distinct. */
 int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, int k, void *stream);

@@ -192,7 +192,11 @@ def read_output_bin(path: str):
         assert magic == b"KMER" and version == 1
         for _ in range(total):
             (id_len,) = struct.unpack("<H", f.read(2))
-            name = f.read(id_len).decode("utf-8")
+            raw = f.read(id_len)
+            try:                                        # feature_extraction.py:121-124
+                name = raw.decode("utf-8")
+            except UnicodeDecodeError:
+                name = "".join(chr(b) if b < 128 else "_" for b in raw)
             (n,) = struct.unpack("<I", f.read(4))
             idx = np.frombuffer(f.read(8 * n), dtype="<u8")
             recs.append((name, sorted(int(x) for x in idx)))

@@ -94,6 +94,43 @@ def test_output_bin_reader_and_metadata(tmp_path):
     assert rn == ["r1", "r1", "second read", "second read", "e", "e"] and st == [0, 1] * 3
 
 
+def test_output_bin_reader_errors_and_edge_records(tmp_path):
+    """feature_extraction.py:109-117 (the reference reader's ValueErrors), empty file sets, non-ASCII ids."""
+    import struct
+    from fedrann_b200.feature_extraction import get_metadata, read_output_bin
+    p = str(tmp_path / "o.bin")
+
+    def put(b):
+        with open(p, "wb") as f:
+            f.write(b)
+
+    put(b"KMER\x01\x00\x00")
+    with pytest.raises(ValueError, match="文件头不完整"):
+        read_output_bin(p)
+    put(b"KMRE\x01\x00\x00\x00" + struct.pack("<Q", 0))
+    with pytest.raises(ValueError, match="无效的文件格式"):
+        read_output_bin(p)
+    put(b"KMER\x02\x00\x00\x00" + struct.pack("<Q", 0))
+    with pytest.raises(ValueError, match="不支持的版本号: 2"):
+        read_output_bin(p)
+    put(b"KMER\x01\x00\x00\x00" + struct.pack("<Q", 0))
+    n, ip, ix = read_output_bin(p)
+    assert n == [] and ip.tolist() == [0] and ix.size == 0 and get_metadata(p, 4) == ([], [])
+    rec = struct.pack("<H", 2) + b"ab" + struct.pack("<I", 2) + struct.pack("<2Q", 3, 1 << 40)
+    put(b"KMER\x01\x00\x00\x00" + struct.pack("<Q", 2) + rec)          # second record missing
+    with pytest.raises(ValueError):
+        read_output_bin(p)
+    put(b"KMER\x01\x00\x00\x00" + struct.pack("<Q", 1) + rec[:-3])     # indices cut short
+    with pytest.raises(ValueError):
+        read_output_bin(p)
+    odd = struct.pack("<H", 3) + b"a\xffb" + struct.pack("<I", 0)          # not UTF-8: bytes >= 128 become '_'
+    utf = struct.pack("<H", 3) + "é1".encode() + struct.pack("<I", 1) + struct.pack("<Q", 7)
+    put(b"KMER\x01\x00\x00\x00" + struct.pack("<Q", 3) + rec + odd + utf)
+    n, ip, ix = read_output_bin(p)
+    assert n == ["ab", "a_b", "é1"] and ip.tolist() == [0, 2, 2, 3] and ix.tolist() == [3, 1 << 40, 7]
+    assert [(a, list(b)) for a, b in O.read_output_bin(p)] == [("ab", [3, 1 << 40]), ("a_b", []), ("é1", [7])]
+
+
 def test_cli_flags_and_defaults():
     from fedrann_b200.__main__ import parse_command_line_arguments
     a = parse_command_line_arguments(["-i", "x.fa", "-o", "out"])
