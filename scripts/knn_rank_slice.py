@@ -5,7 +5,7 @@ rank searches its own N/G query rows against it (pipeline.run_hot_path: q0 = ran
     python scripts/knn_rank_slice.py c4                 -> 6 M x 256, k = 20, 8 ranks (whole-human HiFi 30x)
     python scripts/knn_rank_slice.py sweep8m            -> 8 M x {64,128,256,512} x {10,50}, 8 ranks
 The job's rows/s at G GPUs is N / (slice time) when the ranks finish together (equal-count shards, same work)."""
-import json, sys
+import json, os, sys
 import torch
 sys.path.insert(0, ".")
 from fedrann_b200.engine import Engine
@@ -18,6 +18,9 @@ def run(eng, N, D, k, G, rank=None):
     g = torch.Generator(device="cuda")
     g.manual_seed(1000 + D // 64)
     X = torch.randn((N, D), device="cuda", generator=g)     # 8 M x 512: 16 GB + 16 GB (En) + 8 GB (Eh) of 180
+    zf = float(os.environ.get("KNN_SLICE_ZERO_FRAC", "0"))   # projected embeddings are 49-67 % exact zeros
+    if zf > 0:
+        X.mul_((torch.rand((N, D), device="cuda", generator=g) >= zf).to(X.dtype))
     En, Eh, norms = eng.normalize(X)
     del X
     torch.cuda.empty_cache()
@@ -45,7 +48,7 @@ def run(eng, N, D, k, G, rank=None):
                       "k6_tflops": round(2.0 * nq * N * D / k6 / 1e9, 1),
                       "k7_ms": round(kt["fr_knn_rerank_kernel"][1], 1), "fallback_rows": fb,
                       "fallback_ms": round(fb_ms, 1), "bit_equal_exact_scan_64_rows": ok,
-                      "db_bytes_fp32_fp16": N * D * 4 + N * Eh.shape[1] * 2}), flush=True)
+                      "db_bytes_fp32_fp16": N * D * 4 + N * Eh.shape[1] * 2, "zero_frac": zf}), flush=True)
     del En, Eh, norms, idx, dist
     torch.cuda.empty_cache()
 
@@ -59,6 +62,11 @@ if __name__ == "__main__":
         for D in (64, 128, 256, 512):
             for k in (10, 50):
                 run(eng, 8_000_000, D, k, 8)
+    elif a and a[0] == "diag":                  # scripts/gpu_knn_diag.sh
+        for z in ("0", "0.6"):
+            os.environ["KNN_SLICE_ZERO_FRAC"] = z
+            for D in (64, 128, 256, 512):
+                run(eng, 2_000_000, D, 10, 8)
     else:
         N, D, k, G = (int(x) for x in a[:4])
         run(eng, N, D, k, G, int(a[4]) if len(a) > 4 else None)
