@@ -70,6 +70,7 @@ struct TcParams {
     const float *norms;
     unsigned int *gthr;        // [nq] per-row threshold shared by all CTAs working on the row (orderable float)
     unsigned long long *dbg;   // optional per-role wait-cycle counters (FR_KNN_DEBUG=1)
+    int exp;                   // FR_KNN_EXP (timing experiments, results invalid): 1 = no filter, 2 = no TMEM loads either
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -256,7 +257,22 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 // among its lanes) and appends at a position it keeps in a register: the two warps of a TMEM
 // lane quadrant fill the row's buffer from opposite ends, so no atomic is needed.
 __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *ptr, int step, int &pos, float thr, uint32_t allow) {
+                                            unsigned long long *ptr, int step, int &pos, float thr, uint32_t allow,
+                                            bool sparse) {
+    // Long streams: once a row's threshold has settled most chunks hold no hit at all, and the largest of
+    // the 16 scores (8 three-input max instructions) answers that for less than a quarter of the mask's
+    // instructions.  `sparse` is warp-uniform (few hits in the previous tile); the mask below is built
+    // only by warps with a lane that has a hit, and gives the same bits either way: v <= thr for all 16
+    // scores means no sign bit of thr - v is set (x - x = +0; scores of lanes with a query row are not NaN).
+    if (sparse) {
+        float m[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+            m[g] = fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
+                         fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3])));
+        const float mx = fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
+        if (!(mx > thr) || !allow) return;
+    }
     // four independent 4-bit chains (a single 16-deep funnel-shift chain is pure latency)
     uint32_t m4[4];
 #pragma unroll
@@ -339,6 +355,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0, seg = 0;
+            int64_t done = 0;
             for (int64_t u = u_begin; u < u_end;) {
                 const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
                 const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
@@ -346,7 +363,15 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 mbar_expect_tx(bAFull, (uint32_t)p.kblks * TC_ABLK);
                 for (int kb = 0; kb < p.kblks; ++kb)
                     tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
-                for (int64_t t = t0; t < t1; ++t) {
+                // Database tiles of a segment are visited in ROTATED order, starting at (tiles this CTA has
+                // done so far) mod (segment length): CTAs advance at the same pace, so all CTAs inside a
+                // full segment ask for database tile (step mod db_tiles) at about the same time and one HBM
+                // read serves them all from L2.  In plain order the CTAs sit at 148 different places of a
+                // database far larger than L2 and K6 is HBM-bound (5.6 TB/s at 2 M x 256).  The epilogue
+                // walks the same order; the neighbour lists do not depend on it (K7 is exact).
+                const int64_t len = t1 - t0, rot = done % len;
+                for (int64_t i = 0; i < len; ++i) {
+                    const int64_t t = t0 + (rot + i < len ? rot + i : rot + i - len);
                     for (int kb = 0; kb < p.kblks; ++kb) {
                         for (int h = 0; h < TC_N / TC_NS; ++h) {
                             mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
@@ -359,6 +384,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     }
                 }
                 u += t1 - t0;
+                done += len;
                 ++seg;
             }
         }
@@ -420,6 +446,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             unsigned long long *buf = p.keys + stream * CAP;
             unsigned long long *ptr = sub ? buf + CAP - 1 : buf;     // this warp's end of the row's buffer
             int mycnt = 0;
+            bool sparse_next = false;
             const uint32_t allow = valid ? 0xFFFFu : 0u;
             if (sub == 0) {
                 // start from whatever the row's other CTAs (or this CTA's earlier segment) reached
@@ -431,7 +458,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 s_thr[row_in_tile] = t0v;
             }
             tc_quad_bar(bar_id);
-            for (int64_t t = t0; t < t1; ++t, ++tile) {
+            const int64_t len = t1 - t0, rot = (int64_t)tile % len;       // the producer's order (tile = tiles done)
+            for (int64_t i = 0; i < len; ++i, ++tile) {
+                const int64_t t = t0 + (rot + i < len ? rot + i : rot + i - len);
                 const uint32_t ab = tile & 1;
                 mbar_wait_t(bTFull + 8 * ab, (tile >> 1) & 1, w0, dbg_on);
                 tc_fence_after();
@@ -446,28 +475,34 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 // TMEM loads run two chunks ahead of the filter: the warp's 8 chunks (alternate 16-column
                 // chunks of the tile) go through two 32-register buffers
                 const int cnt_at_tile_start = mycnt;
+                const bool sparse = sparse_next;
                 uint32_t a0[TC_CH], a1[TC_CH], b0[TC_CH], b1[TC_CH];
                 static_assert(TC_EPQ == 2 && TC_N / TC_CH == 16, "chunk schedule below assumes 2 warps x 8 chunks");
+                const bool do_ld = p.exp < 2, do_flt = p.exp < 1;
+                if (do_ld) {
                 tc_ld16(taddr + sub * TC_CH, a0);
                 tc_ld16(taddr + (sub + 2) * TC_CH, a1);
+                }
 #pragma unroll 1
                 for (int c = sub; c < TC_N / TC_CH; c += 8) {
                     long long tq = dbg_on ? clock64() : 0;
                     tc_ld_wait();                                          // a0, a1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
+                    if (do_ld) {
                     tc_ld16(taddr + (c + 4) * TC_CH, b0);
                     tc_ld16(taddr + (c + 6) * TC_CH, b1);
-                    tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
-                    tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
+                    }
+                    if (do_flt) tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
+                    if (do_flt) tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();                                          // b0, b1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
-                    if (c + 8 < TC_N / TC_CH) {
+                    if (do_ld && c + 8 < TC_N / TC_CH) {
                         tc_ld16(taddr + (c + 8) * TC_CH, a0);
                         tc_ld16(taddr + (c + 10) * TC_CH, a1);
                     }
-                    tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
-                    tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow);
+                    if (do_flt) tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
+                    if (do_flt) tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
@@ -477,6 +512,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     n_hits += __reduce_add_sync(0xFFFFFFFFu, dh);
                     n_hitmax += __reduce_max_sync(0xFFFFFFFFu, dh);
                 }
+                // the next tile takes the max-first filter when this one had at most a hit per chunk
+                sparse_next = __reduce_add_sync(0xFFFFFFFFu, mycnt - cnt_at_tile_start) <= TC_N / TC_CH / TC_EPQ;
                 s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
@@ -987,10 +1024,11 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     p.db0 = 0; p.db_end = n_db;
     p.ws_off = 0; p.slot_base = 0;
 
-    p.dbg = tc_debug_buffer(st);
+    p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
     rc = tc_launch_k6(ctx, S, p, st);
     if (rc) return rc;
     if (p.dbg) tc_debug_report(p, p.dbg, st);
+    if (p.exp) return FR_OK;          // timing experiment: K6 only, no neighbour lists
     return tc_finish(ctx, S, d_En, d_norms, D, q0, nq, k, 4096, d_idx, d_dist, st);
 }
 
@@ -1063,7 +1101,7 @@ extern "C" int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream) {
         p.q0 = a; p.nq = b - a;
         p.db0 = 0; p.db_end = b;
         p.ws_off = a; p.slot_base = 0;
-        p.dbg = tc_debug_buffer(st);
+        p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
         int rc = tc_launch_k6(ctx, inc->S, p, st);
         if (rc) return rc;
         if (p.dbg) {
@@ -1078,7 +1116,7 @@ extern "C" int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream) {
         p.q0 = 0; p.nq = a;
         p.db0 = a; p.db_end = b;
         p.ws_off = 0; p.slot_base = inc->base_b[j];
-        p.dbg = tc_debug_buffer(st);
+        p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
         int rc = tc_launch_k6(ctx, inc->S, p, st);
         if (rc) return rc;
         if (p.dbg) {
