@@ -70,7 +70,6 @@ struct TcParams {
     const float *norms;
     unsigned int *gthr;        // [nq] per-row threshold shared by all CTAs working on the row (orderable float)
     unsigned long long *dbg;   // optional per-role wait-cycle counters (FR_KNN_DEBUG=1)
-    int exp;                   // FR_KNN_EXP (timing experiments, results invalid): 1 = no filter, 2 = no TMEM loads either
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -256,23 +255,8 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 // per score).  Each lane then walks ITS OWN set bits (the warp's cost is the largest hit count
 // among its lanes) and appends at a position it keeps in a register: the two warps of a TMEM
 // lane quadrant fill the row's buffer from opposite ends, so no atomic is needed.
-__device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
-                                            unsigned long long *ptr, int step, int &pos, float thr, uint32_t allow,
-                                            bool sparse) {
-    // Long streams: once a row's threshold has settled most chunks hold no hit at all, and the largest of
-    // the 16 scores (8 three-input max instructions) answers that for less than a quarter of the mask's
-    // instructions.  `sparse` is warp-uniform (few hits in the previous tile); the mask below is built
-    // only by warps with a lane that has a hit, and gives the same bits either way: v <= thr for all 16
-    // scores means no sign bit of thr - v is set (x - x = +0; scores of lanes with a query row are not NaN).
-    if (sparse) {
-        float m[4];
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-            m[g] = fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
-                         fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3])));
-        const float mx = fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
-        if (!(mx > thr) || !allow) return;
-    }
+__device__ __forceinline__ uint32_t tc_mask16(const uint32_t (&v)[16], uint32_t cbase, bool ragged, int64_t n_db,
+                                              float thr, uint32_t allow) {
     // four independent 4-bit chains (a single 16-deep funnel-shift chain is pure latency)
     uint32_t m4[4];
 #pragma unroll
@@ -289,6 +273,11 @@ __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cb
         const int64_t left = n_db - (int64_t)cbase;
         mask = left >= 16 ? mask : (left <= 0 ? 0u : (mask & ((1u << left) - 1)));
     }
+    return mask;
+}
+
+__device__ __forceinline__ void tc_walk16(const uint32_t (&v)[16], uint32_t mask, uint32_t cbase,
+                                          unsigned long long *ptr, int step, int &pos) {
     while (mask) {
         // the value is picked from the registers by a 4-level select tree on the bits of j
         // (no dynamic register indexing)
@@ -304,6 +293,34 @@ __device__ __forceinline__ void tc_filter16(const uint32_t (&v)[16], uint32_t cb
         ptr[step * pos] = tc_key(__uint_as_float(x), cbase + j);
         ++pos;
     }
+}
+
+__device__ __forceinline__ float tc_max16(const uint32_t (&v)[16]) {
+    float m[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        m[g] = fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
+                     fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3])));
+    return fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3]));
+}
+
+// Two chunks (the pair of TMEM loads that landed together) in one step: the max-first test is one branch per
+// 32 scores.
+// Long streams: once a row's threshold has settled most chunks hold no hit at all, and the largest of the
+// scores (three-input max instructions, half an instruction per score) answers that for a quarter of the
+// mask's instructions.  `sparse` is warp-uniform (few hits in the previous tile); the masks are then built
+// only by warps with a lane that has a hit, and give the same bits either way: v <= thr for every score
+// means no sign bit of thr - v is set (x - x = +0; scores of lanes with a query row are not NaN).
+__device__ __forceinline__ void tc_filter_pair(const uint32_t (&va)[16], const uint32_t (&vb)[16], uint32_t cbase_a,
+                                               uint32_t cbase_b, bool ragged, int64_t n_db, unsigned long long *ptr,
+                                               int step, int &pos, float thr, uint32_t allow, bool sparse) {
+    if (sparse) {
+        const float mx = fmaxf(tc_max16(va), tc_max16(vb));
+        if (!(mx > thr) || !allow) return;
+    }
+    // one chunk at a time (building both masks first costs registers where hits are frequent: c2 +6 %)
+    tc_walk16(va, tc_mask16(va, cbase_a, ragged, n_db, thr, allow), cbase_a, ptr, step, pos);
+    tc_walk16(vb, tc_mask16(vb, cbase_b, ragged, n_db, thr, allow), cbase_b, ptr, step, pos);
 }
 
 // ---------------------------------------------------------------- K6
@@ -478,31 +495,26 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 const bool sparse = sparse_next;
                 uint32_t a0[TC_CH], a1[TC_CH], b0[TC_CH], b1[TC_CH];
                 static_assert(TC_EPQ == 2 && TC_N / TC_CH == 16, "chunk schedule below assumes 2 warps x 8 chunks");
-                const bool do_ld = p.exp < 2, do_flt = p.exp < 1;
-                if (do_ld) {
                 tc_ld16(taddr + sub * TC_CH, a0);
                 tc_ld16(taddr + (sub + 2) * TC_CH, a1);
-                }
 #pragma unroll 1
                 for (int c = sub; c < TC_N / TC_CH; c += 8) {
                     long long tq = dbg_on ? clock64() : 0;
                     tc_ld_wait();                                          // a0, a1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
-                    if (do_ld) {
                     tc_ld16(taddr + (c + 4) * TC_CH, b0);
                     tc_ld16(taddr + (c + 6) * TC_CH, b1);
-                    }
-                    if (do_flt) tc_filter16(a0, (uint32_t)(col0 + c * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
-                    if (do_flt) tc_filter16(a1, (uint32_t)(col0 + (c + 2) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
+                    tc_filter_pair(a0, a1, (uint32_t)(col0 + c * TC_CH), (uint32_t)(col0 + (c + 2) * TC_CH), ragged,
+                                       p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();                                          // b0, b1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
-                    if (do_ld && c + 8 < TC_N / TC_CH) {
+                    if (c + 8 < TC_N / TC_CH) {
                         tc_ld16(taddr + (c + 8) * TC_CH, a0);
                         tc_ld16(taddr + (c + 10) * TC_CH, a1);
                     }
-                    if (do_flt) tc_filter16(b0, (uint32_t)(col0 + (c + 4) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
-                    if (do_flt) tc_filter16(b1, (uint32_t)(col0 + (c + 6) * TC_CH), ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
+                    tc_filter_pair(b0, b1, (uint32_t)(col0 + (c + 4) * TC_CH), (uint32_t)(col0 + (c + 6) * TC_CH),
+                                       ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
@@ -1024,11 +1036,10 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     p.db0 = 0; p.db_end = n_db;
     p.ws_off = 0; p.slot_base = 0;
 
-    p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
+    p.dbg = tc_debug_buffer(st);
     rc = tc_launch_k6(ctx, S, p, st);
     if (rc) return rc;
     if (p.dbg) tc_debug_report(p, p.dbg, st);
-    if (p.exp) return FR_OK;          // timing experiment: K6 only, no neighbour lists
     return tc_finish(ctx, S, d_En, d_norms, D, q0, nq, k, 4096, d_idx, d_dist, st);
 }
 
@@ -1101,7 +1112,7 @@ extern "C" int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream) {
         p.q0 = a; p.nq = b - a;
         p.db0 = 0; p.db_end = b;
         p.ws_off = a; p.slot_base = 0;
-        p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
+        p.dbg = tc_debug_buffer(st);
         int rc = tc_launch_k6(ctx, inc->S, p, st);
         if (rc) return rc;
         if (p.dbg) {
@@ -1116,7 +1127,7 @@ extern "C" int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream) {
         p.q0 = 0; p.nq = a;
         p.db0 = a; p.db_end = b;
         p.ws_off = 0; p.slot_base = inc->base_b[j];
-        p.dbg = tc_debug_buffer(st); p.exp = getenv("FR_KNN_EXP") ? atoi(getenv("FR_KNN_EXP")) : 0;
+        p.dbg = tc_debug_buffer(st);
         int rc = tc_launch_k6(ctx, inc->S, p, st);
         if (rc) return rc;
         if (p.dbg) {
