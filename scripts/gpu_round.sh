@@ -1,15 +1,21 @@
 #!/bin/bash
-# one GPU call: parity tests, bench, ncu launch list, ncu --set full of the hot kernels
+# one GPU call: parity tests, bench (c2, reference arm, c3), per-rank slice of the 8-GPU config, ncu launch list,
+# ncu --set full of the hot kernels -- most important first, so that a cut-off call still leaves the evidence
 set -x
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
+tail -3 gpurun_out/pytest_gpu.log
 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench rc=$?"
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_c2_ref.json 2> gpurun_out/bench_c2_ref.err; echo "ref rc=$?"
+timeout 120 python scripts/knn_rank_slice.py c4 > gpurun_out/c4_rank_slice.jsonl 2> gpurun_out/c4_rank_slice.err; echo "c4 rc=$?"
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
-for K in fr_knn_tc_kernel fr_extract_kernel fr_knn_rerank_kernel fr_project_kernel; do
+for K in fr_knn_tc_kernel fr_extract_kernel; do
+  ncu --set full --clock-control none --import-source on -k regex:$K -s 3 -c 1 -f -o gpurun_out/prof_$K $CMD > gpurun_out/ncu_$K.log 2>&1
+done
+timeout 200 python bench.py --workload c3 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "c3 rc=$?"
+for K in fr_knn_rerank_kernel fr_project_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$K -s 3 -c 1 -f -o gpurun_out/prof_$K $CMD > gpurun_out/ncu_$K.log 2>&1
 done
 ls -la gpurun_out
