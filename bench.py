@@ -15,6 +15,8 @@ e2e     through fedrann_b200.pipeline.run_hot_path_host: pinned host reads in,
         neighbour lists out to pinned host memory, copies inside the timed region
 roofline        the kernel with the largest share of the step, timed per launch
                 with CUDA event pairs inside libfedrann_b200.so (fr_profile_*)
+stage_rooflines the extract (hashing) and project (SpMM) kernels against the HBM roofline,
+                same algorithmic-byte definitions
 cpu_baseline    the reference's CPU pipeline on the box's host cores, bounded sample
 --impl reference   that CPU pipeline alone, same metric/config
 """
@@ -379,6 +381,18 @@ def main():
             top = max(ktimes, key=lambda k: ktimes[k][1])
             traffic = json.load(open(tp)).get(top, {}).get("dram_bytes_per_launch")
     roof = roofline(ktimes, args.steps, wl, res, w, world_eff, peaks, traffic, ms_per_step)
+    # the hashing and SpMM stages against the HBM roofline as well (north star: "achieved HBM GB/s for the
+    # hashing and SpMM stages"), same definition of algorithmic bytes; never allowed to break the line
+    stage_roofs = {}
+    for kn in ("fr_extract_kernel", "fr_project_kernel"):
+        try:
+            tr = None
+            tp = join(ROOT, "profiles", "ncu_traffic.json")
+            if args.workload == "c2" and world == 1 and isfile(tp):
+                tr = json.load(open(tp)).get(kn, {}).get("dram_bytes_per_launch")
+            stage_roofs[kn] = roofline(ktimes, args.steps, wl, res, w, world_eff, peaks, tr, ms_per_step, name=kn)
+        except Exception as e:      # noqa: BLE001
+            stage_roofs[kn] = {"error": repr(e)}
 
     # ---- CPU baseline (rank 0, N=1 only)
     cpu = None
@@ -394,7 +408,8 @@ def main():
                 "data": "synthetic", "config": config, "clocks": clk,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(hd[0].item()),
                         "d2h_bytes_per_step": int(hd[1].item())},
-                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+                "gpu_launches": int(launches), "roofline": roof, "stage_rooflines": stage_roofs,
+                "cpu_baseline": cpu,
                 "stage_ms": stage_ms,
                 "kernels_ms_per_step": {k: v[1] / args.steps for k, v in ktimes.items()},
                 "knn_fallback_rows": eng.knn_fallback_rows}
@@ -405,11 +420,13 @@ def main():
     return 0
 
 
-def roofline(ktimes, steps, wl, res, w, world, peaks, ncu_traffic, ms_per_step):
-    """Algorithmic bytes/flops per launch (DESIGN.md 'Kernels') / measured launch duration."""
-    if not ktimes:
+def roofline(ktimes, steps, wl, res, w, world, peaks, ncu_traffic, ms_per_step, name=None):
+    """Algorithmic bytes/flops per launch (DESIGN.md 'Kernels') / measured launch duration, for the
+    kernel with the largest share of the step or for the one named."""
+    if not ktimes or (name is not None and name not in ktimes):
         return None
-    name = max(ktimes, key=lambda k: ktimes[k][1])
+    if name is None:
+        name = max(ktimes, key=lambda k: ktimes[k][1])
     n_launch, tot_ms = ktimes[name]
     ms = tot_ms / n_launch
     R = wl.n_reads_local
