@@ -64,17 +64,20 @@ struct FastxCount { int64_t R = 0, B = 0, NL = 0; };
 // For FASTA a range that starts at a header line is independent of what precedes it, so large
 // inputs are parsed by several threads (ranges cut at "\n>"); with emit set the outputs are
 // written at the given record / base / name offsets.
-FastxCount fastx_range(const char *text, int64_t beg, int64_t end, bool is_fastq, bool emit, uint8_t *bases_out,
-                       int64_t *offsets_out, char *names_out, FastxCount at) {
+// A FASTQ record that starts inside the range takes its three following lines even where they lie past
+// `end` (lines are read up to text_end); *stop = where the state machine stands, between records, when it
+// leaves the range -- the next range is independent of this one exactly when it starts there.
+FastxCount fastx_range(const char *text, int64_t beg, int64_t end, int64_t text_end, bool is_fastq, bool emit,
+                       uint8_t *bases_out, int64_t *offsets_out, char *names_out, FastxCount at, int64_t *stop) {
     int64_t R = at.R, B = at.B, NL = at.NL;
     bool have_rec = false;  // FASTA: a record with a non-empty id is open
     int64_t pos = beg;
     auto next_line = [&](int64_t &ls, int64_t &le) -> bool {
-        if (pos >= end) return false;
+        if (pos >= text_end) return false;
         ls = pos;
-        const void *nl = memchr(text + pos, '\n', (size_t)(end - pos));
-        le = nl ? (const char *)nl - text : end;
-        pos = nl ? le + 1 : end;
+        const void *nl = memchr(text + pos, '\n', (size_t)(text_end - pos));
+        le = nl ? (const char *)nl - text : text_end;
+        pos = nl ? le + 1 : text_end;
         return true;
     };
     auto open_rec = [&](const char *id, int64_t idlen) {
@@ -86,7 +89,7 @@ FastxCount fastx_range(const char *text, int64_t beg, int64_t end, bool is_fastq
         NL += idlen + 1;
     };
     int64_t ls, le;
-    while (next_line(ls, le)) {
+    while (pos < end && next_line(ls, le)) {
         if (le == ls) continue;                                                     // :168
         if (!is_fastq) {
             if (text[ls] == '>') {
@@ -112,6 +115,7 @@ FastxCount fastx_range(const char *text, int64_t beg, int64_t end, bool is_fastq
         }
     }
     if (!is_fastq && have_rec) ++R;
+    if (stop) *stop = pos;
     FastxCount out;
     out.R = R - at.R; out.B = B - at.B; out.NL = NL - at.NL;
     return out;
@@ -132,36 +136,74 @@ extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases
     if (const char *e = getenv("FR_PARSE_THREADS")) threads = atoi(e);
     if (const char *e = getenv("FR_PARSE_MIN_RANGE")) min_range = atoll(e);
     if (min_range < 1) min_range = 1;
-    if (threads < 1 || is_fastq) threads = 1;
+    if (threads < 1) threads = 1;
     if ((int64_t)threads > text_len / min_range) threads = (int)(text_len / min_range);
     if (threads < 1) threads = 1;
+    // line [a, b) starting at p (b excludes the newline); false at the end of the text
+    auto line_at = [&](int64_t p, int64_t &b, int64_t &next) -> bool {
+        if (p >= text_len) return false;
+        const void *nl = memchr(text + p, '\n', (size_t)(text_len - p));
+        b = nl ? (const char *)nl - text : text_len;
+        next = nl ? b + 1 : text_len;
+        return true;
+    };
     std::vector<int64_t> cut(1, 0);
     for (int t = 1; t < threads; ++t) {
         int64_t p = text_len / threads * t;
         if (p < cut.back()) p = cut.back();
         int64_t c = -1;
-        while (p < text_len) {                       // next "\n>"
+        if (!is_fastq) {
+            while (p < text_len) {                       // next "\n>"
+                const void *nl = memchr(text + p, '\n', (size_t)(text_len - p));
+                if (!nl) break;
+                p = (const char *)nl - text + 1;
+                if (p < text_len && text[p] == '>') { c = p; break; }
+            }
+        } else {
+            // FASTQ: a line start that looks like a record start -- '@' line, a non-empty line, a '+' line and
+            // a line as long as the second (a quality line that begins with '@' fails the '+' test).  It is a
+            // guess; the ranges are only used when every range ends where the next one starts (below).
             const void *nl = memchr(text + p, '\n', (size_t)(text_len - p));
-            if (!nl) break;
-            p = (const char *)nl - text + 1;
-            if (p < text_len && text[p] == '>') { c = p; break; }
+            int64_t q = nl ? (const char *)nl - text + 1 : text_len;
+            for (int tries = 0; tries < 64 && q < text_len && c < 0; ++tries) {
+                int64_t b0, n0, b1, n1, b2, n2, b3, n3;
+                if (!line_at(q, b0, n0)) break;
+                if (text[q] == '@' && line_at(n0, b1, n1) && b1 > n0 && line_at(n1, b2, n2) && b2 > n1 &&
+                    text[n1] == '+' && line_at(n2, b3, n3) && b3 - n2 == b1 - n0)
+                    c = q;
+                q = n0;
+            }
         }
-        if (c < 0) break;
+        if (c < 0) { if (is_fastq) continue; else break; }
         if (c > cut.back()) cut.push_back(c);
     }
     cut.push_back(text_len);
-    const int nr = (int)cut.size() - 1;
+    int nr = (int)cut.size() - 1;
     std::vector<FastxCount> cnt(nr), at(nr + 1);
+    std::vector<int64_t> stop(nr, 0);
     auto run = [&](bool do_emit) {
         std::vector<std::thread> th;
         for (int t = 1; t < nr; ++t)
             th.emplace_back([&, t] {
-                cnt[t] = fastx_range(text, cut[t], cut[t + 1], is_fastq, do_emit, bases_out, offsets_out, names_out, at[t]);
+                cnt[t] = fastx_range(text, cut[t], cut[t + 1], text_len, is_fastq, do_emit, bases_out, offsets_out,
+                                     names_out, at[t], &stop[t]);
             });
-        cnt[0] = fastx_range(text, cut[0], cut[1], is_fastq, do_emit, bases_out, offsets_out, names_out, at[0]);
+        cnt[0] = fastx_range(text, cut[0], cut[1], text_len, is_fastq, do_emit, bases_out, offsets_out, names_out,
+                             at[0], &stop[0]);
         for (auto &x : th) x.join();
     };
     run(false);
+    if (is_fastq) {
+        // range t + 1 was parsed as if a record could start at cut[t + 1]; that is what the sequential reader
+        // does only if range t stops exactly there.  Otherwise (odd input): one range, sequentially.
+        bool ok = true;
+        for (int t = 0; t + 1 < nr; ++t) ok = ok && stop[t] == cut[t + 1];
+        if (!ok) {
+            cut.assign({0, text_len});
+            nr = 1;
+            run(false);
+        }
+    }
     for (int t = 0; t < nr; ++t) {
         at[t + 1].R = at[t].R + cnt[t].R; at[t + 1].B = at[t].B + cnt[t].B; at[t + 1].NL = at[t].NL + cnt[t].NL;
     }

@@ -125,8 +125,52 @@ def test_fasta_parse_in_parallel_ranges_equals_oracle(monkeypatch, threads, min_
         b2, o2, n2 = reads_to_arrays(O.parse_fastx(text))
         b, o, n = engine.parse_fastx(text)
         assert n == n2 and np.array_equal(o, o2) and b.tobytes() == b2.tobytes()
-    # FASTQ stays on one thread ('@' may start a quality line)
+    # FASTQ whose quality lines begin with '@'
     fq = b"".join(b"@q%d\nACGT\n+\n@@@@\n" % i for i in range(200))
     b2, o2, n2 = reads_to_arrays(O.parse_fastx(fq))
     b, o, n = engine.parse_fastx(fq)
     assert n == n2 and np.array_equal(o, o2) and b.tobytes() == b2.tobytes()
+
+
+def _tricky_fastq(nrec, seed, odd):
+    """Four-line records with quality lines that may begin with '@' or '+'; with `odd` also blank lines, junk
+    lines between records, wrapped / truncated records and a missing final newline (inputs on which a guessed
+    range start can be wrong: the parser must then give the sequential answer all the same)."""
+    r = np.random.default_rng(seed)
+    qual = np.frombuffer(b"@+!IJK#5", dtype=np.uint8)
+    dna = np.frombuffer(b"ACGTNacgt", dtype=np.uint8)
+    parts = []
+    for i in range(nrec):
+        L = int(r.integers(1, 60))
+        seq = bytes(r.choice(dna, size=L))
+        q = bytes(r.choice(qual, size=L))
+        parts.append(b"@r%d desc %d\n" % (i, L) + seq + b"\n+" + (b"r%d" % i if r.integers(0, 3) == 0 else b"") + b"\n" + q + b"\n")
+        if odd:
+            kind = r.integers(0, 12)
+            if kind == 0:
+                parts.append(b"\n")
+            elif kind == 1:
+                parts.append(b"junk line\n")
+            elif kind == 2:
+                parts.append(b"@cut%d\nACGT\n" % i)                  # a record without its last two lines
+            elif kind == 3:
+                parts.append(b"@wrap%d\nACGT\nACGT\n+\n@@@@\n@@@@\n" % i)   # wrapped sequence and quality
+            elif kind == 4:
+                parts.append(b"@e%d\n\n+\n\n" % i)                 # empty sequence
+    text = b"".join(parts)
+    return text[:-1] if odd and seed % 2 else text
+
+
+@pytest.mark.parametrize("threads,min_range", [(1, 1 << 30), (7, 64), (16, 1), (3, 1000)])
+@pytest.mark.parametrize("odd", [False, True])
+def test_fastq_parse_in_parallel_ranges_equals_oracle(monkeypatch, threads, min_range, odd):
+    """FASTQ ranges start at guessed record starts and are used only when every range stops where the next one
+    starts; in every case the records are those of the sequential reader (kmer_searcher.cpp:188-194)."""
+    from fedrann_b200 import engine
+    monkeypatch.setenv("FR_PARSE_THREADS", str(threads))
+    monkeypatch.setenv("FR_PARSE_MIN_RANGE", str(min_range))
+    for seed in range(6):
+        text = _tricky_fastq(250, seed, odd)
+        b2, o2, n2 = reads_to_arrays(O.parse_fastx(text))
+        b, o, n = engine.parse_fastx(text)
+        assert n == n2 and np.array_equal(o, o2) and b.tobytes() == b2.tobytes()
