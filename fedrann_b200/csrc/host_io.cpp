@@ -242,10 +242,16 @@ extern "C" int fr_write_output_bin(const char *path, const char *names, const in
         put(id, (size_t)idlen);
         uint32_t cnt = (uint32_t)(indptr[r + 1] - indptr[r]);
         put(&cnt, 4);
-        for (int64_t t = indptr[r]; t < indptr[r + 1]; ++t) {
-            uint64_t v = (uint64_t)(uint32_t)indices[t];
-            put(&v, 8);
+        // the row's indices widened to u64 in place at the end of the buffer (one resize per row, not one
+        // insert per index: the reference's per-index ofstream::write, :125-128, is what made this file slow)
+        const size_t at = buf.size(), nb = 8 * (size_t)cnt;
+        buf.resize(at + nb);
+        char *dst = buf.data() + at;
+        for (int64_t t = indptr[r]; t < indptr[r + 1]; ++t, dst += 8) {
+            const uint64_t v = (uint64_t)(uint32_t)indices[t];
+            memcpy(dst, &v, 8);
         }
+        if (buf.size() >= (1u << 22)) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
     }
     if (!buf.empty()) fwrite(buf.data(), 1, buf.size(), f);
     fclose(f);
