@@ -60,7 +60,10 @@ int fr_library_parse(const char *text, int64_t text_len, int k, uint64_t *codes_
 
 /* kmer_searcher.cpp:153-201.  FASTA/FASTQ text -> concatenated bases +
  * offsets + names.  Two-call protocol: with bases_out == NULL only the counts
- * are returned.  names_out receives the names separated by '\n'. */
+ * are returned.  names_out receives the names separated by '\n'.  Large
+ * inputs are parsed by several host threads (FASTA: ranges cut at header
+ * lines; FASTQ: ranges at guessed record starts, used only when consistent
+ * with the sequential reader); the records are always the sequential ones. */
 int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64_t *offsets_out,
                    char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len);
 
