@@ -4,6 +4,7 @@
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 
 import torch
@@ -14,7 +15,8 @@ from .engine import Engine
 # Gather the fp32 rows on a side stream while K6 runs (parallel.all_gather_rows(overlap=True)).
 # Off by default: measured on 4 x B200 the NCCL kernel and the persistent K6 CTAs compete for SMs
 # (K6 +8 %) and the step gets slower; at 2 ranks it gains 7 %.
-OVERLAP_ROW_GATHER = False
+# FEDRANN_OVERLAP_GATHER=1 turns it on for a run (chr1 scale on 8 ranks: the gather is 9.9 ms of 74).
+OVERLAP_ROW_GATHER = os.environ.get("FEDRANN_OVERLAP_GATHER", "0") == "1"
 
 
 @dataclass
