@@ -465,8 +465,10 @@ def roofline(ktimes, steps, wl, res, w, world, peaks, ncu_traffic, ms_per_step, 
 
 
 def _roof(bound, achieved, peak, unit, kernel, ms, per_step, traffic, src, share):
+    # traffic_gbps: the kernel's measured DRAM traffic (ncu capture) over its live launch duration
     return {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak,
-            "traffic": traffic, "kernel": kernel, "kernel_ms": ms, "launches_per_step": per_step,
+            "traffic": traffic, "traffic_gbps": (traffic / 1e9 / (ms / 1e3)) if traffic and ms > 0 else None,
+            "kernel": kernel, "kernel_ms": ms, "launches_per_step": per_step,
             "share_of_step": share, "peak_source": src}
 
 
