@@ -13,7 +13,8 @@ _HERE = dirname(abspath(__file__))
 LIB_PATH = join(_HERE, "libfedrann_b200.so")
 
 FR_OK = 0
-_ERR = {-1: "FR_ERR_CUDA", -2: "FR_ERR_ARG", -3: "FR_ERR_STATE", -4: "FR_ERR_NOMEM", -5: "FR_ERR_NO_DEVICE"}
+_ERR = {-1: "FR_ERR_CUDA", -2: "FR_ERR_ARG", -3: "FR_ERR_STATE", -4: "FR_ERR_NOMEM", -5: "FR_ERR_NO_DEVICE",
+        -6: "FR_ERR_IO", -7: "FR_ERR_BAD_ID", -8: "FR_ERR_UNVERIFIED"}
 
 SYMBOLS = [
     "fr_version", "fr_create", "fr_destroy", "fr_last_error", "fr_launch_count",

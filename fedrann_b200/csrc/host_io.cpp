@@ -218,8 +218,9 @@ extern "C" int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases
 
 extern "C" int fr_write_output_bin(const char *path, const char *names, const int64_t *name_offsets, int64_t n_reads,
                                    const int64_t *indptr, const int32_t *indices) {
+    if (!path || !name_offsets || !indptr || n_reads < 0) return FR_ERR_ARG;
     FILE *f = fopen(path, "wb");
-    if (!f) return FR_ERR_ARG;
+    if (!f) return FR_ERR_IO;
     std::vector<char> buf;
     buf.reserve(1 << 22);
     auto put = [&](const void *p, size_t n) {
@@ -236,10 +237,12 @@ extern "C" int fr_write_output_bin(const char *path, const char *names, const in
         const char *id = names + name_offsets[r];
         const int64_t idlen = name_offsets[r + 1] - name_offsets[r];
         for (int64_t j = 0; j < idlen; ++j)
-            if (id[j] < 32 || id[j] > 126) rc = FR_ERR_ARG;       // :112-116 (the reference throws)
+            if (id[j] < 32 || id[j] > 126) rc = FR_ERR_BAD_ID;    // :112-116 (the reference throws)
+        // :118-120: the length is stored in 16 bits and exactly that many id bytes follow (an id longer
+        // than 65535 bytes is truncated consistently, as the reference does)
         uint16_t l16 = (uint16_t)idlen;
         put(&l16, 2);
-        put(id, (size_t)idlen);
+        put(id, (size_t)l16);
         uint32_t cnt = (uint32_t)(indptr[r + 1] - indptr[r]);
         put(&cnt, 4);
         // the row's indices widened to u64 in place at the end of the buffer (one resize per row, not one
@@ -301,7 +304,7 @@ extern "C" int fr_read_output_bin(const unsigned char *blob, int64_t len, char *
 
 extern "C" int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features) {
     FILE *f = fopen(path, "wb");
-    if (!f) return FR_ERR_ARG;
+    if (!f) return FR_ERR_IO;
     for (int64_t i = 0; i < n_features; ++i) {
         if (!docfreq[i]) continue;                                   // :217
         uint64_t rec[2] = {(uint64_t)i, (uint64_t)docfreq[i]};
@@ -350,7 +353,7 @@ extern "C" int fr_write_overlaps_tsv(const char *path, int append, const char *n
                                      const float *dist, int64_t *lines_out) {
     if (!path || !names || !name_offsets || n_rows < 0 || k < 0 || (n_rows > 0 && (!idx || !dist))) return FR_ERR_ARG;
     FILE *f = fopen(path, append ? "ab" : "wb");
-    if (!f) return FR_ERR_ARG;
+    if (!f) return FR_ERR_IO;
     std::vector<char> buf;
     buf.reserve((1u << 22) + 4096);
     if (!append) {

@@ -131,7 +131,8 @@ int main(int argc, char *argv[]) {
     if (fr_write_frequency_bin((out_dir + "/kmer_frequency.bin").c_str(), docfreq.data(), n_codes) != FR_OK) return 1;
     const int rc = fr_write_output_bin((out_dir + "/output.bin").c_str(), names.empty() ? "" : names.data(),
                                        name_off.data(), R, indptr.data(), indices.data());
-    if (rc == FR_ERR_ARG) { fprintf(stderr, "terminate: ID contains non-ASCII characters\n"); return 134; }
+    if (rc == FR_ERR_BAD_ID) { fprintf(stderr, "terminate: ID contains non-ASCII characters\n"); return 134; }
+    if (rc == FR_ERR_IO) fprintf(stderr, "Failed to open output file: %s/output.bin\n", out_dir.c_str());
     fr_destroy(ctx);
     return rc == FR_OK ? 0 : 1;
 }

@@ -87,7 +87,7 @@ extern "C" int fr_table_set_sampler(fr_ctx *ctx, uint64_t seed, uint64_t thresho
                                  cudaMemcpyDeviceToHost, st));
     FR_CUDA(ctx, cudaStreamSynchronize(st));
     if (ctx->h_counters[3] != 0)
-        return fr_fail(ctx, FR_ERR_ARG, "fr_table_set_sampler: the library is not a sample of this sampler");
+        return fr_fail(ctx, FR_ERR_UNVERIFIED, "fr_table_set_sampler: the library is not a sample of this sampler");
     ctx->table.sampled = 1;
     ctx->table.seed = seed;
     ctx->table.threshold = threshold;

@@ -68,7 +68,8 @@ def write_output_bin(path: str, names, indptr: np.ndarray, indices: np.ndarray) 
     rc = L.fr_write_output_bin(path.encode(), C.c_char_p(blob), noff.ctypes.data_as(C.c_void_p), len(enc),
                                indptr.ctypes.data_as(C.c_void_p), indices.ctypes.data_as(C.c_void_p))
     if rc != 0:
-        raise FedrannError("ID contains non-ASCII characters" if rc == -2 else f"fr_write_output_bin: {rc}")
+        raise FedrannError("ID contains non-ASCII characters" if rc == -7 else
+                           f"cannot open {path}" if rc == -6 else f"fr_write_output_bin: {rc}")
 
 
 def write_frequency_bin(path: str, docfreq: np.ndarray) -> None:
@@ -147,7 +148,10 @@ class Engine:
         return out
 
     def dev(self, a: np.ndarray, dtype=None) -> torch.Tensor:
-        t = torch.from_numpy(np.ascontiguousarray(a))
+        a = np.ascontiguousarray(a)
+        if not a.flags.writeable:           # torch.from_numpy refuses to alias read-only memory silently
+            a = a.copy()
+        t = torch.from_numpy(a)
         if dtype is not None:
             t = t.to(dtype)
         return t.to(f"cuda:{self.device}", non_blocking=True)
@@ -198,7 +202,7 @@ class Engine:
             seed, fraction = sampler
             thr = min(int(fraction * 2.0 ** 64), 2 ** 64 - 1)
             rc = self.L.fr_table_set_sampler(self.h, seed & (2 ** 64 - 1), thr, _stream())
-            if rc not in (0, -2):
+            if rc not in (0, -8):                      # -8 = FR_ERR_UNVERIFIED: not such a sample, generic path
                 check(self.h, rc, "fr_table_set_sampler")
             self.sampled = rc == 0
 

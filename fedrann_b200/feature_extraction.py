@@ -80,11 +80,17 @@ def get_feature_matrix(ks_file: str, precompute_matrix, kmer_count: int, read_co
     if len(names) != read_count:
         logger.debug("output.bin holds %d records, read_count is %d", len(names), read_count)
     nk = int(kmer_count) // 2
-    # the reference's set -> COO -> CSR conversion sorts and de-duplicates columns
+    # The reference builds A_chunk through COO (feature_extraction.py:191-205), which SORTS the columns of a
+    # row; a (row, column) pair listed twice would be summed there (int8 value 2).  kmer_searcher writes a set
+    # per read (robin_hood::unordered_set, kmer_searcher.cpp:94), so a valid output.bin has no duplicates;
+    # a file that does is refused rather than silently de-duplicated.
     rows = np.repeat(np.arange(len(names), dtype=np.int64), np.diff(indptr))
-    key = np.unique(rows * np.int64(max(int(kmer_count), 1) + 1) + indices)
-    rows_u = key // np.int64(max(int(kmer_count), 1) + 1)
-    cols_u = (key % np.int64(max(int(kmer_count), 1) + 1)).astype(np.int32)
+    stride = np.int64(max(int(kmer_count), 1) + 1)
+    key = np.sort(rows * stride + indices)
+    if len(key) > 1 and bool((key[1:] == key[:-1]).any()):
+        raise ValueError("output.bin lists a feature index twice in one record (kmer_searcher never writes that)")
+    rows_u = key // stride
+    cols_u = (key % stride).astype(np.int32)
     ip = np.zeros(len(names) + 1, dtype=np.int64)
     np.cumsum(np.bincount(rows_u, minlength=len(names)), out=ip[1:])
     P_dev = eng.upload_projection(precompute_matrix)

@@ -22,6 +22,25 @@ class _NearestNeighbors:
         raise NotImplementedError()
 
 
+MAX_NEIGHBORS = 128          # FR_MAX_K of csrc/knn_exact.cu: list length of the exact scan and of the fallback
+TC_MAX_DIM = 512             # query tile resident in shared memory (csrc/knn_tc.cu TC_MAX_KBLKS * 64)
+
+
+def check_knn_limits(n_neighbors: int, dim: int) -> None:
+    """Limits of the exact backend, checked before any work is done (the reference's pynndescent takes
+    any n_neighbors; INTEGRATION.md lists the difference).  Dimensions above 512 are answered by the
+    fp32 CUDA-core scan (same lists, ~100x slower than the tensor-core path): warned about, not refused."""
+    from .custom_logging import logger
+    if int(n_neighbors) > MAX_NEIGHBORS:
+        raise ValueError(f"--nndescent-n-neighbors / index_n_neighbors = {n_neighbors}: the exact kNN backend "
+                         f"returns at most {MAX_NEIGHBORS} neighbours per row")
+    if int(n_neighbors) < 1:
+        raise ValueError("n_neighbors must be at least 1")
+    if int(dim) > TC_MAX_DIM:
+        logger.warning("embedding dimension %d > %d: the kNN stage runs the fp32 scan on the CUDA cores instead "
+                       "of the tensor-core path (same neighbour lists, far slower)", dim, TC_MAX_DIM)
+
+
 def _device_knn(eng, E: torch.Tensor, k: int, q0: int = 0, nq: int | None = None, mode: int = 0):
     En, Eh, norms = eng.normalize(E)
     return eng.knn(En, Eh, norms, k, q0=q0, nq=nq, mode=mode)
@@ -55,6 +74,7 @@ class NNDescent_ava(_NearestNeighbors):
         else:
             E = eng.dev(np.ascontiguousarray(data, dtype=np.float32))
         n = E.shape[0]
+        check_knn_limits(index_n_neighbors, E.shape[1])
         k = min(int(index_n_neighbors), n)
         idx, dist = _device_knn(eng, E, k)
         torch.cuda.synchronize()

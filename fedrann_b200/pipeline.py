@@ -54,6 +54,7 @@ class HotPathResult:
     nbr_idx: torch.Tensor            # (2R, k) int32, global row ids
     nbr_dist: torch.Tensor           # (2R, k) fp32
     row_offset: int                  # global row id of this rank's first embedding row
+    db: tuple | None = None          # (En, Eh, norms) of the WHOLE database the search ran against
 
 
 def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev, nk: int, k_nn: int,
@@ -83,7 +84,7 @@ def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev,
     k_eff = min(k_nn, En.shape[0])
     idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None)
     t.stop()
-    return HotPathResult(indptr, indices, E, idx, dist, q0)
+    return HotPathResult(indptr, indices, E, idx, dist, q0, (En, Eh, norms))
 
 
 @dataclass
@@ -262,7 +263,7 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
         indices = torch.cat([ix[:n_c] for ix, n_c in zip(ixs, nz)]) if ixs else torch.zeros(0, dtype=torch.int32, device=dev)
     else:
         torch.cuda.current_stream().synchronize()
-    return HotPathResult(indptr, indices, E, idx, dist, q0)
+    return HotPathResult(indptr, indices, E, idx, dist, q0, (En, Eh, norms))
 
 
 _pinned: dict = {}

@@ -30,6 +30,9 @@ extern "C" {
 #define FR_ERR_STATE (-3)     /* call order violated (e.g. fill before count)  */
 #define FR_ERR_NOMEM (-4)     /* device allocation failed                      */
 #define FR_ERR_NO_DEVICE (-5) /* no usable sm_100 device                       */
+#define FR_ERR_IO (-6)        /* a file could not be opened / written           */
+#define FR_ERR_BAD_ID (-7)    /* a read id holds a non-printable byte (the reference throws, kmer_searcher.cpp:112-116) */
+#define FR_ERR_UNVERIFIED (-8) /* fr_table_set_sampler: the library is not such a sample (nothing changes) */
 
 typedef struct fr_ctx fr_ctx;
 
@@ -68,7 +71,9 @@ int fr_fastx_parse(const char *text, int64_t text_len, uint8_t *bases_out, int64
                    char *names_out, int64_t *n_reads, int64_t *n_bases, int64_t *names_len);
 
 /* kmer_searcher.cpp:98-130 and 203-229: output.bin / kmer_frequency.bin
- * writers (rows in input order, indices ascending). */
+ * writers (rows in input order, indices ascending).  FR_ERR_IO when the file cannot be created,
+ * FR_ERR_BAD_ID for a non-printable id byte; ids longer than 65535 bytes are truncated to
+ * (length mod 65536) bytes exactly as the reference's uint16 cast does (:118-120). */
 int fr_write_output_bin(const char *path, const char *names, const int64_t *name_offsets,
                         int64_t n_reads, const int64_t *indptr, const int32_t *indices);
 int fr_write_frequency_bin(const char *path, const uint32_t *docfreq, int64_t n_features);
@@ -94,7 +99,7 @@ int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, int k, void 
  * the sampling rule of csrc/common.cuh (`fr_sample_keep`: a 32-bit murmur-style mix of the
  * k-mer and the seed, compared with the top 32 bits of threshold; everything passes at
  * threshold = 2^64 - 1), which is how N1 (fr_kmer_count_*) samples.  The claim is
- * VERIFIED on the device for every key; FR_ERR_ARG (and no change of behaviour) when it does not
+ * VERIFIED on the device for every key; FR_ERR_UNVERIFIED (and no change of behaviour) when it does not
  * hold.  When it holds, extraction rejects positions whose canonical k-mer fails the same test
  * in registers; results are identical either way. */
 int fr_table_set_sampler(fr_ctx *ctx, uint64_t seed, uint64_t threshold, void *stream);
