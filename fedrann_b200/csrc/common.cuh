@@ -86,6 +86,7 @@ struct fr_ctx {
     void *d_knn_fb = nullptr;       // exact distances of the fallback rows (parallel fallback)
     int64_t knn_fb_cap = 0;
     int64_t knn_fallback_rows = 0;
+    int knn_last_path = -1;         // 0 = tcgen05 pass + re-rank, 1 = fp32 scan (fr_knn_last_path)
     bool knn_fb_pending = false;    // h_counters[4] holds the count once knn_fb_stream has drained
     cudaStream_t knn_fb_stream = nullptr;
     void *knn_inc = nullptr;        // state of an incremental search (fr_knn_inc_*), owned by knn_tc.cu

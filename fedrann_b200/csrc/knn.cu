@@ -25,6 +25,7 @@ extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const fl
         int rc = fr_knn_wait_rows(ctx, st);
         if (rc) return rc;
     }
+    ctx->knn_last_path = 1;
     if (mode == 1)
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     if (mode != 0) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode must be 0 or 1");
@@ -47,6 +48,8 @@ int fr_knn_wait_rows(fr_ctx *ctx, cudaStream_t st) {
     }
     return FR_OK;
 }
+
+extern "C" int fr_knn_last_path(const fr_ctx *ctx) { return ctx ? ctx->knn_last_path : -1; }
 
 extern "C" int64_t fr_knn_last_fallback_rows(fr_ctx *ctx) {
     if (!ctx) return 0;

@@ -1024,6 +1024,7 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
         if (rcw) return rcw;
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     }
+    ctx->knn_last_path = 0;
     TcSetup S;
     TcParams geo{};
     const int slots = tc_geometry(ctx, geo, nq, n_db);
@@ -1090,6 +1091,7 @@ extern "C" int fr_knn_inc_begin(fr_ctx *ctx, const float *d_En, const void *d_Eh
     }
     ctx->knn_fallback_rows = 0;
     ctx->knn_fb_pending = false;
+    ctx->knn_last_path = 0;
     int rc = tc_setup(ctx, inc->S, d_Eh, d_norms, n_db, Dp, k, n_db, total, st);
     if (rc) { tc_inc_free(inc); ctx->knn_inc = nullptr; return rc; }
     return FR_OK;

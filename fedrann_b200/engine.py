@@ -329,5 +329,10 @@ class Engine:
         return D <= 512 and k <= 128 and N >= 2 * k and N < 2 ** 31 - 256
 
     @property
+    def knn_last_path(self) -> str:
+        """'tcgen05' or 'scan': the path the last kNN call actually took"""
+        return {0: "tcgen05", 1: "scan"}.get(int(self.L.fr_knn_last_path(self.h)), "none")
+
+    @property
     def knn_fallback_rows(self) -> int:
         return int(self.L.fr_knn_last_fallback_rows(self.h))

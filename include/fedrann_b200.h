@@ -168,6 +168,9 @@ int fr_knn_inc_phase(fr_ctx *ctx, int j, void *stream);
 int fr_knn_inc_finish(fr_ctx *ctx, int32_t *d_idx, float *d_dist, void *stream);
 /* statistics of the last fr_knn call: rows that needed the exact fallback */
 int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
+/* which path the last fr_knn / fr_knn_inc_begin took: 0 = tensor-core pass + fp32 re-rank, 1 = fp32 scan on the
+ * CUDA cores (mode 1, or a shape outside the tensor-core path: D > 512, k > 128, n_db < 2k); -1 before any call */
+int fr_knn_last_path(const fr_ctx *ctx);
 
 /* ---- N1: canonical k-mer counting + seeded sampling ----
  * Replaces the pre-step of run_kmer_searcher (fedrann/count_kmers.py:76-123:

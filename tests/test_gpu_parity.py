@@ -413,3 +413,104 @@ def test_host_path_redoes_chunks_that_overflow(eng):
     assert torch.equal(a.indptr, b.indptr) and torch.equal(a.indices, b.indices)
     assert torch.equal(a.nbr_idx.cpu(), b.nbr_idx.cpu()) and torch.equal(a.nbr_dist.cpu(), b.nbr_dist.cpu())
     assert torch.equal(hb.nbr_idx, a.nbr_idx.cpu())
+
+
+# ---------------------------------------------------------------------------
+# kNN at the sizes of the BASELINE configurations (the regimes the small cases above never reach:
+# a database far larger than L2 with the rotated tile order, several candidate buffers per row,
+# the bounded merge of K7).  The whole answer cannot be checked by the CPU oracle in seconds, so
+# seeded blocks of query rows are re-answered by the exact fp32 scan (fr_knn mode 1, itself pinned
+# to the oracle by test_knn_vs_oracle) and must agree bit for bit.
+# ---------------------------------------------------------------------------
+def _clustered_rows(N, D, seed, n_centres=None, noise=0.35, zero_frac=0.5):
+    """Unit-ish rows with real neighbourhoods (reads overlapping the same locus) and the exact zeros
+    projected embeddings have."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    n_centres = n_centres or max(1, N // 40)
+    C = torch.randn((n_centres, D), device="cuda", generator=g)
+    a = torch.randint(0, n_centres, (N,), device="cuda", generator=g)
+    X = C[a] + noise * torch.randn((N, D), device="cuda", generator=g)
+    X[torch.rand((N, D), device="cuda", generator=g) < zero_frac] = 0
+    return X
+
+
+def _check_blocks_vs_scan(eng, En, Eh, norms, k, idx, dist, q0, nq, seed, blocks=4, rows=64):
+    rng = np.random.default_rng(seed)
+    checked = 0
+    for o in sorted(set(int(x) for x in rng.integers(0, max(1, nq - rows + 1), blocks))):
+        n = min(rows, nq - o)
+        ei, ed = eng.knn(En, Eh, norms, k, q0=q0 + o, nq=n, mode=1)
+        assert torch.equal(ei, idx[o:o + n]), "neighbour ids differ from the exact scan at rows %d.." % (q0 + o)
+        assert torch.equal(ed.view(torch.int32), dist[o:o + n].view(torch.int32))
+        checked += n
+    return checked
+
+
+def test_knn_c2_shape_50k_x_500(eng):
+    """BASELINE configs[1] shape: 50 000 rows x D = 500, k = 50 (the reference's defaults -n 500,
+    --nndescent-n-neighbors 50, fedrann/__main__.py:124-141) must take the tensor-core path."""
+    N, D, k = 50_000, 500, 50
+    X = _clustered_rows(N, D, 21)
+    X[77] = 0
+    En, Eh, norms = eng.normalize(X)
+    del X
+    idx, dist = eng.knn(En, Eh, norms, k)
+    assert eng.knn_last_path == "tcgen05"
+    fb = eng.knn_fallback_rows
+    assert _check_blocks_vs_scan(eng, En, Eh, norms, k, idx, dist, 0, N, 1) >= 192
+    assert fb < N // 100
+    # ascending distances, self first for non-zero rows
+    assert bool((dist[:, 1:] >= dist[:, :-1]).all())
+    nz = norms > 0
+    assert bool((idx[nz, 0] == torch.arange(N, device="cuda", dtype=torch.int32)[nz]).float().mean() > 0.999)
+
+
+def test_knn_1m_x_256_database_slice(eng):
+    """chr1-scale database (1 M x 256, BASELINE configs[2]); one rank's query slice of an 8-way split
+    (rows [q0, q0 + nq) of the same array): the fp16 copy is 0.5 GB >> L2, every CTA streams it in the
+    rotated order, a query tile is shared by several CTAs (several candidate buffers per row)."""
+    N, D, k = 1_000_000, 256, 50
+    X = _clustered_rows(N, D, 22, n_centres=N // 60)
+    En, Eh, norms = eng.normalize(X)
+    del X
+    q0, nq = 371_234, 12_345          # unaligned on purpose
+    idx, dist = eng.knn(En, Eh, norms, k, q0=q0, nq=nq)
+    assert eng.knn_last_path == "tcgen05"
+    assert _check_blocks_vs_scan(eng, En, Eh, norms, k, idx, dist, q0, nq, 2, blocks=3, rows=48) >= 96
+    assert eng.knn_fallback_rows < 50
+
+
+def test_knn_many_phase_incremental_200k_bounded_merge(eng):
+    """A 24-phase incremental search over 200 000 rows: every row ends with dozens of candidate buffers,
+    far more keys than K7's merge area (2 x CAP), so the filtered merge (rr_merge_filtered: keys below the
+    row's shared threshold - 2 eps are dropped while merging) is what produces the answer."""
+    N, D, k = 200_000, 64, 20
+    X = _clustered_rows(N, D, 23, n_centres=N // 50, zero_frac=0.3)
+    En, Eh, norms = eng.normalize(X)
+    del X
+    cuts = np.linspace(0, N, 25).astype(np.int64)
+    cuts[1:-1] += np.random.default_rng(3).integers(-500, 500, 23)      # unaligned phase bounds
+    eng.knn_inc_begin(En, Eh, norms, k, [int(c) for c in cuts])
+    for j in range(24):
+        eng.knn_inc_phase(j)
+    idx, dist = eng.knn_inc_finish()
+    fb = eng.knn_fallback_rows
+    assert _check_blocks_vs_scan(eng, En, Eh, norms, k, idx, dist, 0, N, 4) >= 192
+    i1, d1 = eng.knn(En, Eh, norms, k)                                   # one-shot search: same bits
+    assert torch.equal(i1, idx) and torch.equal(d1.view(torch.int32), dist.view(torch.int32))
+    assert fb < N // 20
+
+
+def test_knn_shapes_outside_the_tensor_core_path_are_reported(eng):
+    """D > 512 is answered by the fp32 scan (same lists); the engine says so instead of silently
+    being ~100x slower, and k > 128 is refused up front."""
+    from fedrann_b200.nearest_neighbors import check_knn_limits
+    X = _clustered_rows(600, 576, 24)
+    En, Eh, norms = eng.normalize(X)
+    i0, d0 = eng.knn(En, Eh, norms, 10)
+    assert eng.knn_last_path == "scan"
+    i1, d1 = eng.knn(En, Eh, norms, 10, mode=1)
+    assert torch.equal(i0, i1) and torch.equal(d0, d1)
+    with pytest.raises(ValueError):
+        check_knn_limits(129, 500)
