@@ -287,17 +287,70 @@ fr_knn_fb_select_kernel(const unsigned long long *__restrict__ keys, int64_t n_d
     }
 }
 
+// First level of the selection: the key array of one fallback query is cut into parts of FR_FB_PART keys;
+// one CTA per part holds its keys in registers and finds the part's k smallest by the same bitwise
+// search (64 block-wide counts, no memory traffic), then writes them (padded with all-ones) for the second
+// level, which is fr_knn_fb_select_kernel over parts x FR_MAX_K keys.  A single CTA searching a million
+// keys 64 times took 11 ms per uncertified row at the chr1 scale; this is ~0.1 ms.
+#define FR_FB_KPT 16
+#define FR_FB_PART (1024 * FR_FB_KPT)
+__global__ void __launch_bounds__(1024)
+fr_knn_fb_part_kernel(const unsigned long long *__restrict__ keys, int64_t n_db, int k,
+                      const unsigned long long *__restrict__ n_rows, int f_base, int fb_max, int parts,
+                      unsigned long long *__restrict__ part_keys) {
+    __shared__ int s_cnt[64];
+    __shared__ int s_n;
+    const int f = blockIdx.y, part = blockIdx.x;
+    if (f >= min((int64_t)(*n_rows) - f_base, (int64_t)fb_max)) return;
+    const unsigned long long *kp = keys + (int64_t)f * n_db;
+    const int64_t base = (int64_t)part * FR_FB_PART;
+    unsigned long long v[FR_FB_KPT];
+#pragma unroll
+    for (int i = 0; i < FR_FB_KPT; ++i) {
+        const int64_t j = base + (int64_t)i * 1024 + threadIdx.x;
+        v[i] = j < n_db ? __ldcg(kp + j) : 0xFFFFFFFFFFFFFFFFull;
+    }
+    if (threadIdx.x < 64) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    unsigned long long X = 0;       // the part's k-th smallest key: the largest x with count(keys < x) <= k - 1
+    for (int b = 63; b >= 0; --b) {
+        const unsigned long long cand = X | (1ull << b);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < FR_FB_KPT; ++i) c += v[i] < cand;
+        c = __reduce_add_sync(0xFFFFFFFFu, c);
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_cnt[b], c);
+        __syncthreads();
+        if (s_cnt[b] <= k - 1) X = cand;
+    }
+    unsigned long long *out = part_keys + ((int64_t)f * parts + part) * FR_MAX_K;
+#pragma unroll
+    for (int i = 0; i < FR_FB_KPT; ++i)
+        if (v[i] <= X && v[i] != 0xFFFFFFFFFFFFFFFFull) {
+            const int q = atomicAdd(&s_n, 1);
+            if (q < FR_MAX_K) out[q] = v[i];
+        }
+    __syncthreads();
+    for (int j = min(s_n, FR_MAX_K) + threadIdx.x; j < FR_MAX_K; j += blockDim.x) out[j] = 0xFFFFFFFFFFFFFFFFull;
+}
+
 int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
                            int k, const int32_t *d_rows, const unsigned long long *d_n_rows, int32_t *d_idx,
                            float *d_dist, int *rows_covered, cudaStream_t st) {
     *rows_covered = 0;
     if (k < 1 || k > FR_MAX_K || n_db < k) return FR_OK;
-    // scratch: fb_max x n_db keys, at most 1 GB
+    // scratch: fb_max x n_db keys, at most 1 GB, then the first-level selections (fb_max x parts x FR_MAX_K keys)
     int fb_max = FR_FB_MAX;
     while (fb_max > 8 && (int64_t)fb_max * n_db * 8 > (1ll << 30)) fb_max >>= 1;
     if ((int64_t)fb_max * n_db * 8 > (1ll << 31)) return FR_OK;
-    int rc = fr_ensure(ctx, &ctx->d_knn_fb, &ctx->knn_fb_cap, (int64_t)fb_max * n_db * 8, "kNN fallback keys");
+    const int parts = (int)((n_db + FR_FB_PART - 1) / FR_FB_PART);
+    const int64_t keys_b = (int64_t)fb_max * n_db * 8;
+    const int64_t part_b = (int64_t)fb_max * parts * FR_MAX_K * 8;
+    int rc = fr_ensure(ctx, &ctx->d_knn_fb, &ctx->knn_fb_cap, keys_b + part_b, "kNN fallback keys");
     if (rc) return rc;
+    unsigned long long *d_keys = (unsigned long long *)ctx->d_knn_fb;
+    unsigned long long *d_part = (unsigned long long *)((unsigned char *)ctx->d_knn_fb + keys_b);
     const size_t smem = (size_t)FR_FB_QB * D * sizeof(float);
     FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_fb_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((unsigned)(ctx->sm_count * 4), (unsigned)((fb_max + FR_FB_QB - 1) / FR_FB_QB));
@@ -306,10 +359,17 @@ int fr_knn_fallback_launch(fr_ctx *ctx, const float *d_En, const float *d_norms,
     for (int b = 0; b < batches; ++b) {
         fr_kt_begin(ctx, "fr_knn_fb_dist_kernel", st);
         fr_knn_fb_dist_kernel<<<grid, 256, smem, st>>>(d_En, d_norms, n_db, D, q0, d_rows, d_n_rows, b * fb_max, fb_max,
-                                                       (unsigned long long *)ctx->d_knn_fb);
+                                                       d_keys);
         FR_LAUNCH_CHECK(ctx, "fr_knn_fb_dist_kernel");
+        if (parts > 1) {
+            fr_kt_begin(ctx, "fr_knn_fb_part_kernel", st);
+            fr_knn_fb_part_kernel<<<dim3((unsigned)parts, (unsigned)fb_max), 1024, 0, st>>>(
+                d_keys, n_db, k, d_n_rows, b * fb_max, fb_max, parts, d_part);
+            FR_LAUNCH_CHECK(ctx, "fr_knn_fb_part_kernel");
+        }
         fr_kt_begin(ctx, "fr_knn_fb_select_kernel", st);
-        fr_knn_fb_select_kernel<<<fb_max, 1024, 0, st>>>((const unsigned long long *)ctx->d_knn_fb, n_db, k, d_rows,
+        fr_knn_fb_select_kernel<<<fb_max, 1024, 0, st>>>(parts > 1 ? d_part : d_keys,
+                                                         parts > 1 ? (int64_t)parts * FR_MAX_K : n_db, k, d_rows,
                                                          d_n_rows, b * fb_max, fb_max, d_idx, d_dist);
         FR_LAUNCH_CHECK(ctx, "fr_knn_fb_select_kernel");
     }

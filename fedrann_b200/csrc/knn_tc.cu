@@ -47,10 +47,13 @@ constexpr int TC_NS = 256;                       // database rows per B stage / 
 constexpr int TC_STAGE = TC_NS * TC_KB * 2;      // 32 KB per B stage
 constexpr int TC_STASH = 0;                      // (no shared-memory stash: hit columns are replayed from registers)
 constexpr int TC_ROWST = TC_M * 4 * (1 + TC_EPQ); // per-row threshold + one append counter per quadrant warp
-constexpr int TC_MAX_STAGES = 8;
+constexpr int TC_MAX_STAGES = 12;
 constexpr int TC_MAX_KBLKS = 8;                  // Dp <= 512 keeps the query tile resident
+constexpr int TC_BAR_BYTES = 16 * TC_MAX_STAGES + 64;   // full[] empty[] a_full a_empty tmem_full[2] tmem_empty[2] tmem slot
 constexpr int TC_MAX_SLOTS = 6;
-constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_NS >> 3) << 17) | ((TC_M >> 4) << 24);  // f16 x f16, K-major
+// instruction descriptor: f16 x f16 -> f32, both operands K-major, N = 256; M = 128 per CTA, or 256 over a CTA pair
+constexpr uint32_t TC_IDESC = (1u << 4) /*D=f32*/ | ((TC_NS >> 3) << 17) | ((TC_M >> 4) << 24);
+constexpr uint32_t TC_IDESC_PAIR = (1u << 4) | ((TC_NS >> 3) << 17) | (((2 * TC_M) >> 4) << 24);
 
 // |fp16-operand score - fp32 score| for unit rows: 2^-10 (two roundings, Cauchy-Schwarz) + fp32
 // accumulation of <= 512 terms + subnormal inputs; see DESIGN.md "kNN certification".
@@ -62,8 +65,9 @@ struct TcParams {
     int64_t ws_off;             // workspace row of query row q0 (0 unless the workspace spans more rows)
     int slot_base;              // first candidate buffer of a row this launch may use
     int kblks, stages;
-    int64_t db_tiles, q_tiles, units;
-    int n_ctas, slots, klo, khi;
+    int64_t db_tiles, q_tiles, units;   // units = (groups of `pair + 1` query tiles) x database tiles
+    int n_ctas, slots, klo, khi;        // n_ctas = persistent workers (CTAs, or CTA pairs when pair == 1)
+    int pair;                           // 1: cta_group::2 -- two CTAs share every database tile (M = 256 per MMA)
     unsigned long long *keys;
     int *counts;
     float *thrs;
@@ -84,17 +88,43 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ uint32_t mbar_try(uint32_t bar, uint32_t parity) {
     uint32_t ok;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(bar), "r"(parity)
-            : "memory");
-    } while (!ok);
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+// A wait that cannot hang the GPU: a barrier that has not completed after ~2 s of SM clocks (every wait of
+// this kernel is microseconds long) traps, which fails the launch instead of blocking the device.
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    while (!mbar_try(bar, parity))
+        if (clock64() - t0 > (1ll << 32)) __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
+}
+// ---- CTA pair (cluster of 2): rank, peer addresses, cluster barrier
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {      // same offset in CTA `rank` of the cluster
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, long long &acc, bool on) {
     if (!on) { mbar_wait(bar, parity); return; }
@@ -108,18 +138,45 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// the same load issued by one CTA of a pair: data into ITS shared memory, completion bytes to the barrier at
+// `bar_cluster` (a shared::cluster address: the leader CTA's barrier)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t bar_cluster, int c0,
+                                                 int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster), "r"(c0), "r"(c1)
+        : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// completion of all MMAs issued so far -> one arrival on the barrier at this offset; for a pair the arrival is
+// multicast to the barrier at the same offset in BOTH CTAs
+template <bool PAIR>
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    if (PAIR)
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(bar), "h"((uint16_t)3) : "memory");
+    else
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// D[tmem] (+)= A[smem] . B[smem]^T.  PAIR: issued by the leader CTA for both -- M = 256 (each CTA's 128 query rows,
+// accumulated in its own TMEM), N = 256 (each CTA holds 128 of the database rows of the tile in its shared memory)
+template <bool PAIR>
 __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate)
-        : "memory");
+    if (PAIR)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(TC_IDESC_PAIR), "r"(accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate)
+            : "memory");
 }
 // K-major operand, 128-byte swizzle: 8-row groups 1024 B apart, descriptor version 1 (sm_100)
 __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
@@ -324,43 +381,61 @@ __device__ __forceinline__ void tc_filter_pair(const uint32_t (&va)[16], const u
 }
 
 // ---------------------------------------------------------------- K6
-template <int CAP>
+// PAIR = true: the kernel is launched in clusters of two CTAs (one TPC) and every tcgen05.mma is a
+// cta_group::2 instruction issued by the pair's leader: the two CTAs hold the query tiles 2g and 2g + 1
+// (128 rows each, resident in their own shared memory, accumulated in their own TMEM) and each loads only
+// HALF of every database tile (128 of its 256 rows); the tensor cores of both SMs read both halves.  Per
+// flop this halves the bytes TMA writes into shared memory and the B-operand bytes each SM reads from it --
+// with one CTA per tile that pipe, not the tensor pipe, is the bound.
+// Barriers of a pair: `full` / `a_full` / `tmem_empty` live in the LEADER (the CTA that issues the MMAs
+// waits on them; the peer's TMA completions and arrivals go there through shared::cluster addresses),
+// `empty` / `a_empty` / `tmem_full` exist in both CTAs and are signalled by multicast commits.
+template <int CAP, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ unsigned char tc_smem_raw[];
+    constexpr int G = PAIR ? 2 : 1;                                  // CTAs per worker
+    constexpr uint32_t STAGE_BYTES = PAIR ? TC_ABLK : TC_STAGE;      // this CTA's share of a database k-block
     const uint32_t raw = smem_u32(tc_smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;
     unsigned char *gbase = tc_smem_raw + (base - raw);
     const uint32_t sA = base;
     const uint32_t sB = sA + p.kblks * TC_ABLK;
-    const uint32_t sStash = sB + p.stages * TC_STAGE;
+    const uint32_t sStash = sB + p.stages * STAGE_BYTES;
     const uint32_t sRow = sStash + TC_STASH;
     const uint32_t sBar = sRow + TC_ROWST;
-    // barriers: full[8] empty[8] a_full a_empty tmem_full[2] tmem_empty[2], then the TMEM base address
-    const uint32_t bFull = sBar, bEmpty = sBar + 64, bAFull = sBar + 128, bAEmpty = sBar + 136,
-                   bTFull = sBar + 144, bTEmpty = sBar + 160;
-    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gbase + (sBar - base) + 176);
+    const uint32_t bFull = sBar, bEmpty = sBar + 8 * TC_MAX_STAGES, bAFull = sBar + 16 * TC_MAX_STAGES,
+                   bAEmpty = bAFull + 8, bTFull = bAFull + 16, bTEmpty = bAFull + 32;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(gbase + (sBar - base) + 16 * TC_MAX_STAGES + 48);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = PAIR ? cluster_ctarank() : 0u;            // 0 = leader
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(bFull + 8 * s, 1); mbar_init(bEmpty + 8 * s, 1); }
-        mbar_init(bAFull, 1);
+        for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(bFull + 8 * s, G); mbar_init(bEmpty + 8 * s, 1); }
+        mbar_init(bAFull, G);
         mbar_init(bAEmpty, 1);
-        for (int b = 0; b < 2; ++b) { mbar_init(bTFull + 8 * b, 1); mbar_init(bTEmpty + 8 * b, 4 * TC_EPQ); }
+        for (int b = 0; b < 2; ++b) { mbar_init(bTFull + 8 * b, 1); mbar_init(bTEmpty + 8 * b, G * 4 * TC_EPQ); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                         smem_u32((const void *)tmem_slot)), "r"(512) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32((const void *)tmem_slot)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32((const void *)tmem_slot)), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();        // the peer's barriers are initialised before anything arrives on them
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    const int cta = blockIdx.x;
+    const int cta = blockIdx.x / G;      // worker: a CTA, or a CTA pair
     const bool dbg_on = p.dbg != nullptr;
     long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0, n_cmp = 0, n_hits = 0, n_hitmax = 0;
     const long long t_start = clock64();
@@ -368,20 +443,30 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     const int64_t u_end = ((int64_t)(cta + 1) * p.units) / p.n_ctas;
 
     if (warp == 0) {
-        // ------------------------------------------------ TMA producer
+        // ------------------------------------------------ TMA producer (one per CTA: its query tile, its share of B)
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0, seg = 0;
             int64_t done = 0;
+            // where completions are counted: this CTA's barriers, or the leader's for a pair
+            const uint32_t rAFull = PAIR ? mapa_u32(bAFull, 0) : bAFull;
+            const uint32_t rFull = PAIR ? mapa_u32(bFull, 0) : bFull;
             for (int64_t u = u_begin; u < u_end;) {
-                const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
+                const int64_t qt = (u / p.db_tiles) * G + crank, t0 = u % p.db_tiles;
                 const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
                 if (seg > 0) mbar_wait(bAEmpty, (seg - 1) & 1);   // previous segment's MMAs are done with A
-                mbar_expect_tx(bAFull, (uint32_t)p.kblks * TC_ABLK);
-                for (int kb = 0; kb < p.kblks; ++kb)
-                    tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
-                // Database tiles of a segment are visited in ROTATED order, starting at (tiles this CTA has
-                // done so far) mod (segment length): CTAs advance at the same pace, so all CTAs inside a
+                if (PAIR) {
+                    if (crank == 0) mbar_expect_tx(bAFull, 2u * (uint32_t)p.kblks * TC_ABLK);
+                    else mbar_arrive_cluster(rAFull);
+                    for (int kb = 0; kb < p.kblks; ++kb)
+                        tma_load_2d_pair(sA + kb * TC_ABLK, &tmap, rAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
+                } else {
+                    mbar_expect_tx(bAFull, (uint32_t)p.kblks * TC_ABLK);
+                    for (int kb = 0; kb < p.kblks; ++kb)
+                        tma_load_2d(sA + kb * TC_ABLK, &tmap, bAFull, kb * TC_KB, (int)(p.q0 + qt * TC_M));
+                }
+                // Database tiles of a segment are visited in ROTATED order, starting at (tiles this worker has
+                // done so far) mod (segment length): workers advance at the same pace, so all workers inside a
                 // full segment ask for database tile (step mod db_tiles) at about the same time and one HBM
                 // read serves them all from L2.  In plain order the CTAs sit at 148 different places of a
                 // database far larger than L2 and K6 is HBM-bound (5.6 TB/s at 2 M x 256).  The epilogue
@@ -390,14 +475,21 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 for (int64_t i = 0; i < len; ++i) {
                     const int64_t t = t0 + (rot + i < len ? rot + i : rot + i - len);
                     for (int kb = 0; kb < p.kblks; ++kb) {
-                        for (int h = 0; h < TC_N / TC_NS; ++h) {
-                            mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
-                            mbar_expect_tx(bFull + 8 * stage, TC_STAGE);
+                        mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
+                        if (PAIR) {
+                            // the pair's stage is complete when both halves have landed: 2 x 16 KB counted on
+                            // the leader's barrier, one arrival from each CTA's producer
+                            if (crank == 0) mbar_expect_tx(bFull + 8 * stage, 2u * STAGE_BYTES);
+                            else mbar_arrive_cluster(rFull + 8 * stage);
+                            tma_load_2d_pair(sB + stage * STAGE_BYTES, &tmap, rFull + 8 * stage, kb * TC_KB,
+                                             (int)(p.db0 + t * TC_N + crank * TC_M));
+                        } else {
+                            mbar_expect_tx(bFull + 8 * stage, STAGE_BYTES);
                             for (int b = 0; b < TC_NS / TC_M; ++b)      // box = 64 x 128 rows
-                                tma_load_2d(sB + stage * TC_STAGE + b * TC_ABLK, &tmap, bFull + 8 * stage, kb * TC_KB,
-                                            (int)(p.db0 + t * TC_N + h * TC_NS + b * TC_M));
-                            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                                tma_load_2d(sB + stage * STAGE_BYTES + b * TC_ABLK, &tmap, bFull + 8 * stage, kb * TC_KB,
+                                            (int)(p.db0 + t * TC_N + b * TC_M));
                         }
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
                 }
                 u += t1 - t0;
@@ -406,8 +498,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // ------------------------------------------------ MMA issuer (the leader's, for a pair)
+        if (lane == 0 && crank == 0) {
             int stage = 0;
             uint32_t phase = 0, seg = 0, tile = 0;
             for (int64_t u = u_begin; u < u_end;) {
@@ -416,25 +508,23 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 mbar_wait(bAFull, seg & 1);
                 for (int64_t t = t0; t < t1; ++t, ++tile) {
                     const uint32_t buf = tile & 1;
-                    mbar_wait_t(bTEmpty + 8 * buf, ((tile >> 1) & 1) ^ 1, w1, dbg_on);   // epilogue drained this accumulator
+                    mbar_wait_t(bTEmpty + 8 * buf, ((tile >> 1) & 1) ^ 1, w1, dbg_on);   // epilogue(s) drained this accumulator
                     tc_fence_after();
                     const uint32_t d_tmem = tmem + buf * TC_N;
                     for (int kb = 0; kb < p.kblks; ++kb) {
                         const uint64_t ad = tc_smem_desc(sA + kb * TC_ABLK);
-                        for (int h = 0; h < TC_N / TC_NS; ++h) {     // two 128-column halves of the accumulator
-                            mbar_wait_t(bFull + 8 * stage, phase, w0, dbg_on);
-                            tc_fence_after();
-                            const uint64_t bd = tc_smem_desc(sB + stage * TC_STAGE);
+                        mbar_wait_t(bFull + 8 * stage, phase, w0, dbg_on);
+                        tc_fence_after();
+                        const uint64_t bd = tc_smem_desc(sB + stage * STAGE_BYTES);
 #pragma unroll
-                            for (int k = 0; k < TC_KB / 16; ++k)
-                                tc_mma(d_tmem + h * TC_NS, ad + 2 * k, bd + 2 * k, (kb | k) != 0);   // +32 B per K=16
-                            tc_commit(bEmpty + 8 * stage);                           // frees the stage when read
-                            if (++stage == p.stages) { stage = 0; phase ^= 1; }
-                        }
+                        for (int k = 0; k < TC_KB / 16; ++k)
+                            tc_mma<PAIR>(d_tmem, ad + 2 * k, bd + 2 * k, (kb | k) != 0);   // +32 B per K=16
+                        tc_commit<PAIR>(bEmpty + 8 * stage);                         // frees the stage when read
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
-                    tc_commit(bTFull + 8 * buf);                                     // accumulator complete
+                    tc_commit<PAIR>(bTFull + 8 * buf);                               // accumulator complete
                 }
-                tc_commit(bAEmpty);
+                tc_commit<PAIR>(bAEmpty);
                 u += t1 - t0;
                 ++seg;
             }
@@ -452,10 +542,13 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         const int bar_id = 1 + quad;
         const int step = sub ? -1 : 1;
         uint32_t tile = 0;
+        // "accumulator drained" is counted where the MMA issuer waits: the leader's barrier for a pair
+        const uint32_t rTEmpty = PAIR ? mapa_u32(bTEmpty, 0) : bTEmpty;
         for (int64_t u = u_begin; u < u_end;) {
-            const int64_t qt = u / p.db_tiles, t0 = u % p.db_tiles;
+            const int64_t qg = u / p.db_tiles, t0 = u % p.db_tiles;
+            const int64_t qt = qg * G + crank;
             const int64_t t1 = min(p.db_tiles, t0 + (u_end - u));
-            const int slot = cta - tc_owner(qt * p.db_tiles, p.units, p.n_ctas);
+            const int slot = cta - tc_owner(qg * p.db_tiles, p.units, p.n_ctas);
             const int64_t grow = qt * TC_M + row_in_tile;
             const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
             const int64_t wrow = valid ? grow + p.ws_off : 0;          // this row in the workspace
@@ -528,7 +621,10 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 sparse_next = __reduce_add_sync(0xFFFFFFFFu, mycnt - cnt_at_tile_start) <= TC_N / TC_CH / TC_EPQ;
                 s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bTEmpty + 8 * ab);
+                if (lane == 0) {
+                    if (PAIR) mbar_arrive_cluster(rTEmpty + 8 * ab);
+                    else mbar_arrive(bTEmpty + 8 * ab);
+                }
                 tc_quad_bar(bar_id);                     // every append of this tile and both counts are visible
                 if (dbg_on) { const long long t2 = clock64(); e_bar += t2 - tb; tb = t2; }
                 // a buffer that could overflow during the next tile is compacted now
@@ -594,9 +690,11 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();        // neither CTA leaves (or frees TMEM) while the pair's MMAs / commits may touch it
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
     }
 }
 
@@ -850,20 +948,31 @@ bool tc_shape_ok(int64_t n_db, int D, int Dp, int k) {
     return !(Dp > TC_MAX_KBLKS * TC_KB || D > 512 || k > 128 || n_db < 2 * (int64_t)k || n_db >= (1ll << 31) - TC_N);
 }
 
-// the persistent-CTA split of nq query rows x ndb database rows; returns the most CTAs that share
-// one query tile (= candidate buffers a row needs for this launch; same arithmetic as tc_owner)
+// should K6 run as CTA pairs (cta_group::2)?  Default yes; FR_KNN_PAIR=0 keeps one CTA per tile (A/B measurements)
+bool tc_pair_mode() {
+    static const int v = getenv("FR_KNN_PAIR") ? atoi(getenv("FR_KNN_PAIR")) : 1;
+    return v != 0;
+}
+
+// the persistent split of nq query rows x ndb database rows over the workers (CTAs, or CTA pairs that take
+// two query tiles at a time); returns the most workers that share one query tile group (= candidate
+// buffers a row needs for this launch; same arithmetic as tc_owner)
 int tc_geometry(const fr_ctx *ctx, TcParams &p, int64_t nq, int64_t ndb) {
+    const int G = tc_pair_mode() ? 2 : 1;
+    p.pair = G - 1;
     p.db_tiles = (ndb + TC_N - 1) / TC_N;
     p.q_tiles = (nq + TC_M - 1) / TC_M;
-    p.units = p.db_tiles * p.q_tiles;
-    int64_t n_ctas = ctx->sm_count;
-    if (n_ctas > 4 * p.q_tiles) n_ctas = 4 * p.q_tiles;
-    if (n_ctas > p.units) n_ctas = p.units;
-    p.n_ctas = (int)n_ctas;
+    const int64_t q_groups = (p.q_tiles + G - 1) / G;
+    p.units = p.db_tiles * q_groups;
+    int64_t n_work = ctx->sm_count / G;
+    if (n_work > 4 * q_groups) n_work = 4 * q_groups;
+    if (n_work > p.units) n_work = p.units;
+    if (n_work < 1) n_work = 1;
+    p.n_ctas = (int)n_work;
     int slots = 1;
-    for (int64_t qt = 0; qt < p.q_tiles; ++qt) {
-        const int64_t a = ((qt * p.db_tiles + 1) * n_ctas - 1) / p.units;
-        const int64_t b = (((qt + 1) * p.db_tiles) * n_ctas - 1) / p.units;
+    for (int64_t qg = 0; qg < q_groups; ++qg) {
+        const int64_t a = ((qg * p.db_tiles + 1) * n_work - 1) / p.units;
+        const int64_t b = (((qg + 1) * p.db_tiles) * n_work - 1) / p.units;
         if ((int)(b - a + 1) > slots) slots = (int)(b - a + 1);
     }
     return slots;
@@ -882,10 +991,11 @@ int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, in
     TcParams &p = S.p;
     p.n_db = n_db;
     p.kblks = Dp / TC_KB;
-    const size_t fixed = 1024 + 256 + TC_STASH + TC_ROWST + (size_t)p.kblks * TC_ABLK;
-    int stages = (int)((232448 - fixed) / TC_STAGE);
+    const size_t fixed = 1024 + TC_BAR_BYTES + TC_STASH + TC_ROWST + (size_t)p.kblks * TC_ABLK;
+    const size_t stage_bytes = tc_pair_mode() ? TC_ABLK : TC_STAGE;     // a pair's CTA stages half of every tile
+    int stages = (int)((232448 - fixed) / stage_bytes);
     p.stages = stages > TC_MAX_STAGES ? TC_MAX_STAGES : stages;
-    S.smem = fixed + (size_t)p.stages * TC_STAGE;
+    S.smem = fixed + (size_t)p.stages * stage_bytes;
     p.slots = slots;
     // a compaction keeps between klo and khi keys: enough beyond k that the k-th and the klo-th
     // score are normally more than 2 eps apart (the K7 certificate), few enough that the running
@@ -926,15 +1036,36 @@ int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, in
 }
 
 // one K6 launch: query rows [q0, q0 + nq) against database rows [db0, db_end); p carries the geometry
+template <int CAP>
+int tc_launch_k6_cap(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st) {
+    if (p.pair) {
+        auto kern = fr_knn_tc_kernel<CAP, true>;
+        FR_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * p.n_ctas));
+        cfg.blockDim = dim3(TC_THREADS);
+        cfg.dynamicSmemBytes = S.smem;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;      // CTA pairs: 2b and 2b + 1 share a TPC
+        at[0].val.clusterDim.x = 2;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        FR_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, S.tmap, p));
+    } else {
+        auto kern = fr_knn_tc_kernel<CAP, false>;
+        FR_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+        kern<<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
+    }
+    return FR_OK;
+}
+
 int tc_launch_k6(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st) {
     fr_kt_begin(ctx, "fr_knn_tc_kernel", st);
-    if (S.cap == 512) {
-        FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
-        fr_knn_tc_kernel<512><<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
-    } else {
-        FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
-        fr_knn_tc_kernel<1024><<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
-    }
+    int rc = S.cap == 512 ? tc_launch_k6_cap<512>(ctx, S, p, st) : tc_launch_k6_cap<1024>(ctx, S, p, st);
+    if (rc) return rc;
     FR_LAUNCH_CHECK(ctx, "fr_knn_tc_kernel");
     return FR_OK;
 }
