@@ -140,14 +140,27 @@ def run_fedrann_pipeline(*, input_path: str, output_dir: str, kmer_size: int, km
     logger.info("--- 4. Nearest Neighbors Search ---")
     logger.info("Exact cosine kNN on the tensor cores (n_neighbors = %d; n_trees = %d is not used)",
                 nndescent_n_neighbors, nndescent_n_trees)
-    En, Eh, norms = eng.normalize(E)
+    from .pipeline import EXCHANGE, _rows_per_rank
+    xch = None
+    if world > 1 and EXCHANGE == "peer":
+        from .parallel import row_exchange
+        xch = row_exchange(eng, _rows_per_rank(E.shape[0], group, None), E.shape[1], group)
+    En, Eh, norms = eng.normalize(E, out=xch.local() if xch is not None else None)
     q0, nq = 0, En.shape[0]
-    if world > 1:
+    if xch is not None:           # peer-memory exchange over NVLink, consumed by the search as it lands
+        xch.pull()
+        En, Eh, norms, q0 = xch.En, xch.Eh, xch.norms, xch.q0
+    elif world > 1:
         En, Eh, norms, q0 = all_gather_rows(En, Eh, norms, group)
     k = min(nndescent_n_neighbors, En.shape[0])
     idx, dstn = eng.knn(En, Eh, norms, k, q0=q0, nq=nq) if nq > 0 and k > 0 else (
         torch.zeros((0, k), dtype=torch.int32), torch.zeros((0, k), dtype=torch.float32))
+    if xch is not None:
+        xch.release()
     idx_h, dist_h = idx.cpu().numpy(), dstn.cpu().numpy()
+    if xch is not None:
+        xch.close()
+        eng._row_exchange = None
 
     nbr_output_file = join(output_dir, "overlaps.tsv")
     logger.debug("Saving overlap table to %s", nbr_output_file)

@@ -24,6 +24,8 @@ SYMBOLS = [
     "fr_knn", "fr_knn_rows_ready_after", "fr_knn_last_fallback_rows", "fr_knn_last_path",
     "fr_knn_inc_begin", "fr_knn_inc_phase", "fr_knn_inc_finish",
     "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
+    "fr_exchange_create", "fr_exchange_connect", "fr_exchange_rows_f32", "fr_exchange_rows_f16", "fr_exchange_norms",
+    "fr_exchange_pull", "fr_exchange_release", "fr_exchange_destroy",
 ]
 
 
@@ -91,6 +93,15 @@ def lib():
     L.fr_kmer_count_add.argtypes = [vp, vp, vp, i64, u64, u64, C.POINTER(i64), vp]
     L.fr_kmer_count_export.argtypes = [vp, i32, vp, vp, i64, C.POINTER(i64), vp]
     L.fr_write_overlaps_tsv.argtypes = [C.c_char_p, i32, vp, vp, i64, i64, i64, i32, vp, vp, C.POINTER(i64)]
+    L.fr_exchange_create.argtypes = [vp, i32, i32, vp, i32, i32, C.POINTER(vp), vp]
+    L.fr_exchange_connect.argtypes = [vp, vp]
+    for fn in (L.fr_exchange_rows_f32, L.fr_exchange_rows_f16, L.fr_exchange_norms):
+        fn.argtypes = [vp]
+        fn.restype = vp
+    L.fr_exchange_pull.argtypes = [vp, vp]
+    L.fr_exchange_release.argtypes = [vp, vp]
+    L.fr_exchange_destroy.argtypes = [vp]
+    L.fr_exchange_destroy.restype = None
     _lib = L
     return L
 

@@ -83,6 +83,12 @@ struct fr_ctx {
     void *d_knn_ws = nullptr;
     int64_t knn_ws_cap = 0;
     cudaEvent_t knn_en_event = nullptr;   // one-shot: the fp32 rows are complete once this event has fired
+    // one-shot (fr_exchange_pull): database shards that are still landing; K6 waits for flags[s] == epoch
+    // before the first tile of shard s (rows [bounds[s], bounds[s+1])), starting at the local shard
+    const uint32_t *knn_shard_flags = nullptr;
+    int knn_n_shards = 0, knn_local_shard = 0;
+    uint32_t knn_shard_epoch = 0;
+    int64_t knn_shard_bounds[FR_MAX_RANKS + 1] = {0};
     void *d_knn_fb = nullptr;       // exact distances of the fallback rows (parallel fallback)
     int64_t knn_fb_cap = 0;
     int64_t knn_fallback_rows = 0;

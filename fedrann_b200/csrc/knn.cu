@@ -26,6 +26,7 @@ extern "C" int fr_knn(fr_ctx *ctx, const float *d_En, const void *d_Eh, const fl
         if (rc) return rc;
     }
     ctx->knn_last_path = 1;
+    if (mode == 1) ctx->knn_shard_flags = nullptr;      // (the scan waited for every row above)
     if (mode == 1)
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
     if (mode != 0) return fr_fail(ctx, FR_ERR_ARG, "fr_knn: mode must be 0 or 1");

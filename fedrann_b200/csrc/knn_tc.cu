@@ -73,6 +73,14 @@ struct TcParams {
     float *thrs;
     const float *norms;
     unsigned int *gthr;        // [nq] per-row threshold shared by all CTAs working on the row (orderable float)
+    // database shards that may still be landing (fr_exchange_pull): shard s = rows [shard_bounds[s], [s+1]) is
+    // complete once flags[s] >= flag_epoch; the local shard is there from the start and the tile order begins
+    // at it (rot_base = its first whole tile).  flags == nullptr: everything is present.
+    const uint32_t *flags;
+    uint32_t flag_epoch;
+    int n_shards, local_shard;
+    int64_t rot_base;
+    int64_t shard_bounds[FR_MAX_RANKS + 1];
     unsigned long long *dbg;   // optional per-role wait-cycle counters (FR_KNN_DEBUG=1)
 };
 
@@ -120,8 +128,13 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {    
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
     return r;
 }
+// Arrival on a barrier of the pair's other CTA (or this CTA's, through the cluster window).  Default
+// semantics (.release at CTA scope), as for a local arrive: a .release.cluster here makes every warp wait for
+// its outstanding global stores (the candidate appends) once per tile -- measured +1 kcycle per tile.  What
+// the arrival orders is TMEM / shared-memory traffic of the tensor pipe, which the tcgen05 fences and the
+// async-proxy completion mechanism cover.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -138,6 +151,21 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// Waits until database shard `s` has landed in local memory (the flag is published by the copy stream of
+// fr_exchange_pull after the shard's peer-to-peer copy); the proxy fence orders the TMA loads that follow
+// after the flag read.  Traps instead of hanging if the shard never arrives.
+__device__ __noinline__ void tc_wait_shard(const uint32_t *flag, uint32_t epoch) {
+    const long long t0 = clock64();
+    while (true) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if ((int32_t)(v - epoch) >= 0) break;
+        if (clock64() - t0 > (16ll << 30)) __trap();
+        __nanosleep(256);
+    }
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
 // the same load issued by one CTA of a pair: data into ITS shared memory, completion bytes to the barrier at
 // `bar_cluster` (a shared::cluster address: the leader CTA's barrier)
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t bar_cluster, int c0,
@@ -448,6 +476,8 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             int stage = 0;
             uint32_t phase = 0, seg = 0;
             int64_t done = 0;
+            const uint32_t all_shards = p.flags ? ((p.n_shards >= 32 ? 0u : (1u << p.n_shards)) - 1u) : 0u;
+            uint32_t ready = p.flags ? (1u << p.local_shard) : 0u;        // shards known to have landed
             // where completions are counted: this CTA's barriers, or the leader's for a pair
             const uint32_t rAFull = PAIR ? mapa_u32(bAFull, 0) : bAFull;
             const uint32_t rFull = PAIR ? mapa_u32(bFull, 0) : bFull;
@@ -471,9 +501,18 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 // read serves them all from L2.  In plain order the CTAs sit at 148 different places of a
                 // database far larger than L2 and K6 is HBM-bound (5.6 TB/s at 2 M x 256).  The epilogue
                 // walks the same order; the neighbour lists do not depend on it (K7 is exact).
-                const int64_t len = t1 - t0, rot = done % len;
+                const int64_t len = t1 - t0, rot = (done + p.rot_base) % len;
                 for (int64_t i = 0; i < len; ++i) {
                     const int64_t t = t0 + (rot + i < len ? rot + i : rot + i - len);
+                    if (ready != all_shards) {
+                        // the rows of this tile belong to shards that may still be on their way over NVLink
+                        const int64_t r0 = p.db0 + t * TC_N, r1 = min(p.db_end, r0 + TC_N);
+                        for (int s = 0; s < p.n_shards; ++s)
+                            if (!((ready >> s) & 1u) && p.shard_bounds[s] < r1 && p.shard_bounds[s + 1] > r0) {
+                                tc_wait_shard(p.flags + s, p.flag_epoch);
+                                ready |= 1u << s;
+                            }
+                    }
                     for (int kb = 0; kb < p.kblks; ++kb) {
                         mbar_wait_t(bEmpty + 8 * stage, phase ^ 1, w0, dbg_on);
                         if (PAIR) {
@@ -568,7 +607,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 s_thr[row_in_tile] = t0v;
             }
             tc_quad_bar(bar_id);
-            const int64_t len = t1 - t0, rot = (int64_t)tile % len;       // the producer's order (tile = tiles done)
+            const int64_t len = t1 - t0, rot = ((int64_t)tile + p.rot_base) % len;   // the producer's order (tile = tiles done)
             for (int64_t i = 0; i < len; ++i, ++tile) {
                 const int64_t t = t0 + (rot + i < len ? rot + i : rot + i - len);
                 const uint32_t ab = tile & 1;
@@ -1120,11 +1159,12 @@ void tc_debug_report(const TcParams &p, unsigned long long *d_dbg, cudaStream_t 
     unsigned long long h[16];
     cudaStreamSynchronize(st);
     cudaMemcpy(h, d_dbg, 128, cudaMemcpyDeviceToHost);
-    const double n = p.n_ctas;
+    const double n = (double)p.n_ctas * (p.pair + 1);      // CTAs that added to the counters
+    fprintf(stderr, "[fr_knn dbg] pair=%d ", p.pair);
     fprintf(stderr, "[fr_knn dbg] per-CTA Mcycles: life %.2f | producer wait-empty %.2f | mma wait-data %.2f wait-tmem %.2f"
                     " | epilogue(avg per warp) wait-acc %.2f busy %.2f | tiles/CTA %.0f\n",
-            h[5] / n / 1e6, h[0] / n / 1e6, h[1] / n / 1e6, h[2] / n / 1e6, h[3] / n / (4e6 * TC_EPQ), h[4] / n / (4e6 * TC_EPQ),
-            (double)p.units / n);
+            h[5] / n / 1e6, h[0] / n / 1e6, h[1] / p.n_ctas / 1e6, h[2] / p.n_ctas / 1e6, h[3] / n / (4e6 * TC_EPQ),
+            h[4] / n / (4e6 * TC_EPQ), (double)p.units / p.n_ctas);
     const double ew = n * 4e6 * TC_EPQ;
     fprintf(stderr, "[fr_knn dbg] epilogue per warp Mcycles: tmem-ld wait %.2f | filter %.2f | quad barriers %.2f | compaction %.2f (%.0f compactions per CTA)\n",
             h[8] / ew, h[9] / ew, h[10] / ew, h[11] / ew, h[12] / n);
@@ -1151,6 +1191,7 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
                      int Dp, int64_t q0, int64_t nq, int k, int32_t *d_idx, float *d_dist, cudaStream_t st) {
     // shapes the tensor-core path does not cover go to the exact scan (same answer, CUDA cores)
     if (!tc_shape_ok(n_db, D, Dp, k)) {
+        ctx->knn_shard_flags = nullptr;      // (the event below fires after every shard has landed)
         int rcw = fr_knn_wait_rows(ctx, st);
         if (rcw) return rcw;
         return fr_knn_exact_launch(ctx, d_En, d_norms, n_db, D, q0, nq, k, nullptr, nullptr, 0, d_idx, d_dist, st);
@@ -1167,6 +1208,16 @@ int fr_knn_tc_launch(fr_ctx *ctx, const float *d_En, const void *d_Eh, const flo
     p.nq = nq; p.q0 = q0;
     p.db0 = 0; p.db_end = n_db;
     p.ws_off = 0; p.slot_base = 0;
+    if (ctx->knn_shard_flags && ctx->knn_n_shards > 1 && ctx->knn_shard_bounds[ctx->knn_n_shards] == n_db) {
+        // shards still landing (fr_exchange_pull): start at the local shard's first whole tile, follow the ring
+        p.flags = ctx->knn_shard_flags;
+        p.flag_epoch = ctx->knn_shard_epoch;
+        p.n_shards = ctx->knn_n_shards;
+        p.local_shard = ctx->knn_local_shard;
+        for (int s = 0; s <= p.n_shards; ++s) p.shard_bounds[s] = ctx->knn_shard_bounds[s];
+        p.rot_base = ((p.shard_bounds[p.local_shard] + TC_N - 1) / TC_N) % p.db_tiles;
+    }
+    ctx->knn_shard_flags = nullptr;
 
     p.dbg = tc_debug_buffer(st);
     rc = tc_launch_k6(ctx, S, p, st);

@@ -38,6 +38,103 @@ def shard_reads(offsets: np.ndarray, world: int) -> np.ndarray:
     return np.array([(R * r) // world for r in range(world + 1)], dtype=np.int64)
 
 
+class _DeviceArray:
+    """CUDA array interface over memory the native library owns (the exchange slab)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class RowExchange:
+    """The embedding database of all ranks exchanged through PEER MEMORY (fr_exchange_*, csrc/exchange.cu):
+    every rank owns a slab with room for ALL rows, writes its own rows into it, and pulls the other shards
+    over NVLink with the copy engines WHILE the search runs (K6 starts on the local shard and waits for a
+    shard's "landed" flag only when it gets there; K7 waits for the fp32 rows).  One instance per
+    (engine, row counts, D); reused every step.
+
+        x = RowExchange(eng, rows_per_rank, D, group)
+        eng.normalize(E, out=x.local())            # this rank's rows straight into the slab
+        x.pull()                                   # barrier + queued peer copies (asynchronous)
+        idx, dist = eng.knn(x.En, x.Eh, x.norms, k, q0=x.q0, nq=x.nq)
+        x.release()                                # nobody overwrites rows a peer still reads
+    """
+
+    def __init__(self, eng, rows_per_rank, D: int, group=None):
+        import ctypes as C
+        self.eng, self.group = eng, group
+        self.world = dist.get_world_size(group) if group is not None else 1
+        self.rank = dist.get_rank(group) if group is not None else 0
+        counts = [int(c) for c in rows_per_rank]
+        assert len(counts) == self.world
+        self.bounds = np.zeros(self.world + 1, dtype=np.int64)
+        np.cumsum(counts, out=self.bounds[1:])
+        self.N, self.D, self.Dp = int(self.bounds[-1]), int(D), (int(D) + 63) // 64 * 64
+        self.q0, self.nq = int(self.bounds[self.rank]), counts[self.rank]
+        L = eng.L
+        h = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        from ._lib import check
+        check(eng.h, L.fr_exchange_create(eng.h, self.rank, self.world, self.bounds.ctypes.data_as(C.c_void_p), self.D,
+                                          self.Dp, C.byref(h), handle), "fr_exchange_create")
+        self.h = h
+        if self.world > 1:
+            mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=f"cuda:{eng.device}")
+            allh = torch.empty(64 * self.world, dtype=torch.uint8, device=mine.device)
+            dist.all_gather_into_tensor(allh, mine, group=group)
+            blob = bytes(allh.cpu().numpy().tobytes())
+            check(eng.h, L.fr_exchange_connect(self.h, C.c_char_p(blob)), "fr_exchange_connect")
+            dist.barrier(group)
+        dev = f"cuda:{eng.device}"
+        n = max(self.N, 1)
+        self.En = torch.as_tensor(_DeviceArray(L.fr_exchange_rows_f32(self.h), (n, self.D), "<f4"), device=dev)[: self.N]
+        self.Eh = torch.as_tensor(_DeviceArray(L.fr_exchange_rows_f16(self.h), (n, self.Dp), "<f2"), device=dev)[: self.N]
+        self.norms = torch.as_tensor(_DeviceArray(L.fr_exchange_norms(self.h), (n,), "<f4"), device=dev)[: self.N]
+
+    def local(self):
+        a, b = self.q0, self.q0 + self.nq
+        return self.En[a:b], self.Eh[a:b], self.norms[a:b]
+
+    def pull(self):
+        from ._lib import check
+        import ctypes as C
+        check(self.eng.h, self.eng.L.fr_exchange_pull(self.h, C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "fr_exchange_pull")
+
+    def release(self):
+        from ._lib import check
+        import ctypes as C
+        check(self.eng.h, self.eng.L.fr_exchange_release(self.h, C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "fr_exchange_release")
+
+    @property
+    def bytes_pulled_per_step(self) -> int:
+        remote = self.N - self.nq
+        return remote * (self.D * 4 + self.Dp * 2 + 4)
+
+    def close(self):
+        if getattr(self, "h", None):
+            torch.cuda.synchronize()
+            if self.world > 1:
+                dist.barrier(self.group)         # no peer is still reading this slab
+            self.En = self.Eh = self.norms = None
+            self.eng.L.fr_exchange_destroy(self.h)
+            self.h = None
+
+
+def row_exchange(eng, rows_per_rank, D: int, group=None) -> RowExchange:
+    """The engine's exchange for this geometry (created on first use, every rank at the same time)."""
+    key = (tuple(int(c) for c in rows_per_rank), int(D))
+    cur = getattr(eng, "_row_exchange", None)
+    if cur is not None and cur[0] == key:
+        return cur[1]
+    if cur is not None:
+        cur[1].close()
+    x = RowExchange(eng, rows_per_rank, D, group)
+    eng._row_exchange = (key, x)
+    return x
+
+
 def all_gather_rows(En: torch.Tensor, Eh: torch.Tensor, norms: torch.Tensor, group=None, counts=None,
                     overlap: bool = False):
     """All-gather row shards of unequal height.  Returns (En_all, Eh_all,

@@ -12,11 +12,13 @@ import torch
 from .engine import Engine
 
 
-# Gather the fp32 rows on a side stream while K6 runs (parallel.all_gather_rows(overlap=True)).
-# Off by default: measured on 4 x B200 the NCCL kernel and the persistent K6 CTAs compete for SMs
-# (K6 +8 %) and the step gets slower; at 2 ranks it gains 7 %.
-# FEDRANN_OVERLAP_GATHER=1 turns it on for a run (chr1 scale on 8 ranks: the gather is 9.9 ms of 74).
-OVERLAP_ROW_GATHER = os.environ.get("FEDRANN_OVERLAP_GATHER", "0") == "1"
+# How the ranks' embedding rows reach each other:
+#   "peer" (default)  parallel.RowExchange: peer-memory pulls over NVLink by the copy engines, consumed by K6 shard
+#                     by shard while it runs (csrc/exchange.cu) -- no collective, no SM taken from the search;
+#   "nccl"            three all_gather_into_tensor calls before the search (round 1; 9.9 ms of a 74 ms step at the
+#                     chr1 scale on 8 ranks), kept for A/B measurements and for boxes without peer access.
+EXCHANGE = os.environ.get("FEDRANN_EXCHANGE", "peer")
+OVERLAP_ROW_GATHER = os.environ.get("FEDRANN_OVERLAP_GATHER", "0") == "1"      # nccl mode: fp32 rows on a side stream
 
 
 @dataclass
@@ -71,11 +73,21 @@ def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev,
     t.start("project")
     E = eng.project(indptr, indices, P_dev, nk)
     t.stop()
+    multi = group is not None and torch.distributed.get_world_size(group) > 1
+    xch = None
+    if multi and EXCHANGE == "peer":
+        from .parallel import row_exchange
+        xch = row_exchange(eng, _rows_per_rank(E.shape[0], group, rows_per_rank), E.shape[1], group)
     t.start("normalize")
-    En, Eh, norms = eng.normalize(E)
+    En, Eh, norms = eng.normalize(E, out=xch.local() if xch is not None else None)
     t.stop()
     q0, nq, ready = 0, En.shape[0], []
-    if group is not None and torch.distributed.get_world_size(group) > 1:
+    if xch is not None:
+        t.start("exchange")          # the barrier + queueing; the transfers themselves run under the search
+        xch.pull()
+        En, Eh, norms, q0 = xch.En, xch.Eh, xch.norms, xch.q0
+        t.stop()
+    elif multi:
         t.start("allgather")
         from .parallel import all_gather_rows
         En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
@@ -83,8 +95,20 @@ def run_hot_path(eng: Engine, bases: torch.Tensor, offsets: torch.Tensor, P_dev,
     t.start("knn")
     k_eff = min(k_nn, En.shape[0])
     idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None)
+    if xch is not None:
+        xch.release()
     t.stop()
     return HotPathResult(indptr, indices, E, idx, dist, q0, (En, Eh, norms))
+
+
+def _rows_per_rank(n_local: int, group, rows_per_rank):
+    """Rows of every rank (rank-major); exchanged once when the caller does not know them."""
+    if rows_per_rank is not None:
+        return [int(c) for c in rows_per_rank]
+    world = torch.distributed.get_world_size(group)
+    out = [None] * world
+    torch.distributed.all_gather_object(out, int(n_local), group=group)
+    return [int(c) for c in out]
 
 
 @dataclass
@@ -227,9 +251,16 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
         idx, dist = eng.knn_inc_finish(out=out)
         q0 = 0
     else:
-        En, Eh, norms = eng.normalize(E)
+        xch = None
+        if multi and EXCHANGE == "peer":
+            from .parallel import row_exchange
+            xch = row_exchange(eng, _rows_per_rank(E.shape[0], group, rows_per_rank), E.shape[1], group)
+        En, Eh, norms = eng.normalize(E, out=xch.local() if xch is not None else None)
         q0, nq, ready = 0, En.shape[0], []
-        if multi:
+        if xch is not None:
+            xch.pull()
+            En, Eh, norms, q0 = xch.En, xch.Eh, xch.norms, xch.q0
+        elif multi:
             from .parallel import all_gather_rows
             En, Eh, norms, q0, *ready = all_gather_rows(En, Eh, norms, group, rows_per_rank, overlap=OVERLAP_ROW_GATHER)
         if direct and (En.shape[0] < k_nn or nq != hb.nbr_idx.shape[0]):
@@ -237,6 +268,8 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
         k_eff = min(k_nn, En.shape[0])
         idx, dist = eng.knn(En, Eh, norms, k_eff, q0=q0, nq=nq, mode=mode, rows_ready=ready[0] if ready else None,
                             out=out)
+        if xch is not None:
+            xch.release()
     mark("knn done")
     if not direct:
         hb.nbr_idx[:, : idx.shape[1]].copy_(idx, non_blocking=True)

@@ -172,6 +172,40 @@ int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
  * CUDA cores (mode 1, or a shape outside the tensor-core path: D > 512, k > 128, n_db < 2k); -1 before any call */
 int fr_knn_last_path(const fr_ctx *ctx);
 
+/* ---- multi-GPU: the embedding database exchanged through peer memory (NVLink), one rank per GPU ----
+ * reads shard over the GPUs, each GPU searches its query rows against ALL rows.  The reference
+ * is a single process (fedrann/feature_extraction.py:235-290 is its only parallel site), so there is no
+ * interface to replace; a host program (C, or the Python host of this repo) drives it like this, once per rank:
+ *   fr_exchange_create   allocates this rank's slab holding the WHOLE database (f32 rows [N, D], f16 rows
+ *                        [N, Dp], norms [N]; N = row_bounds[world], rank r owns rows [row_bounds[r],
+ *                        row_bounds[r+1])) and returns its CUDA IPC handle (FR_IPC_HANDLE_BYTES bytes);
+ *   (the caller gives every rank every handle: any transport -- MPI, sockets, torch.distributed)
+ *   fr_exchange_connect  maps the peers' slabs (handles of all `world` ranks, rank-major);
+ *   per step:  write the local rows into the slab (fr_normalize with the fr_exchange_rows_* pointers offset to
+ *              the local row range), then
+ *     fr_exchange_pull     crosses a flag barrier over peer memory (every rank's rows are written) and queues
+ *                          the peer-to-peer copies of every remote shard on a copy stream (copy engines: no SM
+ *                          is taken from the search), fp16 rows first in ring order, each followed by a
+ *                          "shard landed" flag, then norms + f32 rows;
+ *     fr_knn               the NEXT fr_knn of the context on the slab's arrays consumes them as they land: the
+ *                          tensor-core pass starts on the local shard and waits for a shard's flag only when
+ *                          it reaches that shard's first tile; the re-rank waits for the f32 rows;
+ *     fr_exchange_release  second barrier: no rank overwrites rows a peer may still be pulling.
+ *   fr_exchange_destroy  after a barrier of the caller's own (peers must have released).
+ * All calls but create / connect / destroy are asynchronous on `stream`. */
+#define FR_MAX_RANKS 16
+#define FR_IPC_HANDLE_BYTES 64
+typedef struct fr_exchange fr_exchange;
+int fr_exchange_create(fr_ctx *ctx, int rank, int world, const int64_t *row_bounds, int D, int Dp,
+                       fr_exchange **out, unsigned char *handle_out);
+int fr_exchange_connect(fr_exchange *x, const unsigned char *handles);
+void *fr_exchange_rows_f32(fr_exchange *x);
+void *fr_exchange_rows_f16(fr_exchange *x);
+void *fr_exchange_norms(fr_exchange *x);
+int fr_exchange_pull(fr_exchange *x, void *stream);
+int fr_exchange_release(fr_exchange *x, void *stream);
+void fr_exchange_destroy(fr_exchange *x);
+
 /* ---- N1: canonical k-mer counting + seeded sampling ----
  * Replaces the pre-step of run_kmer_searcher (fedrann/count_kmers.py:76-123:
  * `jellyfish count -C`, `jellyfish dump -L <min-mult>`, the awk sampler).
