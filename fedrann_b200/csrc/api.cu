@@ -117,7 +117,7 @@ extern "C" int fr_create(int device, fr_ctx **out) {
 extern "C" void fr_destroy(fr_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->d_bloom); cudaFree(ctx->d_slots); cudaFree(ctx->d_cslots);
+    cudaFree(ctx->d_bloom); cudaFree(ctx->d_cores); cudaFree(ctx->d_slots); cudaFree(ctx->d_cslots);
     cudaFree(ctx->d_scratch); cudaFree(ctx->d_spill); cudaFree(ctx->d_read_off);
     cudaFree(ctx->d_read_cnt); cudaFree(ctx->d_read_order); cudaFree(ctx->d_counters); cudaFree(ctx->d_scan_tmp);
     cudaFree(ctx->d_knn_ws); cudaFree(ctx->d_knn_fb); cudaFree(ctx->d_count_slots);

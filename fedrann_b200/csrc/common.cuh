@@ -34,6 +34,12 @@ struct FrTable {
     // registers, without touching the filter.
     int sampled;
     uint64_t seed, threshold;
+    // Core bitmap (K3a first stage): the k-mers ending at `core_w` consecutive positions all contain the
+    // (k - core_w + 1)-mer ending at the FIRST of them; bit `core` is set iff some library k-mer contains that
+    // core at one of the core_w offsets.  One probe (a 32-byte L2 sector, index = the core itself when
+    // 2 * core_c <= core_lg, a multiplicative hash of it otherwise) rejects core_w positions at once.
+    const uint32_t *cores;
+    int core_w, core_c, core_lg, core_hashed;
 };
 
 struct fr_ctx {
@@ -44,6 +50,7 @@ struct fr_ctx {
 
     // K2
     uint32_t *d_bloom = nullptr;
+    uint32_t *d_cores = nullptr;
     uint4 *d_slots = nullptr;
     uint64_t *d_cslots = nullptr;
     FrTable table{};
@@ -125,6 +132,10 @@ __device__ __forceinline__ uint64_t fr_hash(uint64_t kmer) {
 }
 __device__ __forceinline__ uint32_t fr_table_slot(uint64_t h, int lg_cap) {
     return (uint32_t)(h >> (64 - lg_cap));
+}
+// index of a core in the core bitmap (see FrTable)
+__host__ __device__ __forceinline__ uint32_t fr_core_index(uint64_t core, int lg, int hashed) {
+    return hashed ? (uint32_t)((core * FR_HASH_MUL) >> (64 - lg)) : (uint32_t)core;
 }
 __device__ __forceinline__ uint64_t fr_splitmix64(uint64_t x) {
     x += 0x9E3779B97F4A7C15ull;

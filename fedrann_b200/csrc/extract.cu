@@ -28,6 +28,7 @@
 #include "common.cuh"
 
 #include <cstdlib>
+#include <cstring>
 
 #define FR_THREADS 128
 #define FR_PPT 32                       // positions per thread per tile
@@ -484,7 +485,69 @@ __device__ __forceinline__ uint32_t fr_filter32_sampled(uint32_t c0, uint32_t c1
     return pass;
 }
 
-template <bool WIDE, bool SAMPLED>
+// K3a, core bitmap (FrTable::cores): the k-mers ending at W consecutive positions j .. j+W-1 all contain the
+// c-mer (c = K - W + 1) that ends at position j, so ONE probe of the bitmap -- index = that core, or a hash of
+// it when it is longer than 14 bases -- rejects W positions at once: 1/W random L2 sectors per position
+// instead of one, and no hash arithmetic per position.  Returns the pass mask (bit 31-j = position j).
+template <int W>
+__device__ __forceinline__ uint32_t fr_core_groups(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint64_t cmask,
+                                                   const uint32_t *__restrict__ cores, int lg, int hashed) {
+    uint32_t pass = 0;
+#pragma unroll
+    for (int g = 0; g < 32 / W; ++g) {
+        const int j = g * W, s = 62 - 2 * j;     // the core ending at position j is (c0:c1:c2:c3) >> s
+        uint32_t lo, hi;
+        if (s >= 32) { lo = __funnelshift_r(c2, c1, s - 32); hi = __funnelshift_r(c1, c0, s - 32); }
+        else { lo = __funnelshift_r(c3, c2, s); hi = __funnelshift_r(c2, c1, s); }
+        const uint64_t core = (((uint64_t)hi << 32) | lo) & cmask;
+        const uint32_t idx = fr_core_index(core, lg, hashed);
+        const uint32_t word = __ldg(cores + (idx >> 5));
+        const uint32_t bit = (word >> (idx & 31)) & 1u;
+        pass |= (0u - bit) & (((1u << W) - 1u) << (32 - W - j));
+    }
+    return pass;
+}
+
+__device__ __forceinline__ uint32_t fr_filter32_core(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                     const FrTable &tb) {
+    const uint64_t cmask = tb.core_c >= 32 ? ~0ull : ((1ull << (2 * tb.core_c)) - 1);
+    switch (tb.core_w) {
+        case 1: return fr_core_groups<1>(c0, c1, c2, c3, cmask, tb.cores, tb.core_lg, tb.core_hashed);
+        case 2: return fr_core_groups<2>(c0, c1, c2, c3, cmask, tb.cores, tb.core_lg, tb.core_hashed);
+        case 4: return fr_core_groups<4>(c0, c1, c2, c3, cmask, tb.cores, tb.core_lg, tb.core_hashed);
+        default: return fr_core_groups<8>(c0, c1, c2, c3, cmask, tb.cores, tb.core_lg, tb.core_hashed);
+    }
+}
+
+// Second stage for a VERIFIED hash-threshold sample (FrTable::sampled): of the few positions the core bitmap
+// let through, only those whose canonical k-mer passes the sampler's test can be in the library -- evaluated
+// in registers, so that they never reach the table.
+__device__ __forceinline__ uint32_t fr_refine_sampled(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t m,
+                                                      int K, uint64_t kmask, uint64_t seed, uint64_t threshold) {
+    if (threshold == 0xFFFFFFFFFFFFFFFFull) return m;
+    const uint32_t seedmix = fr_sample_seedmix(seed), thr32 = (uint32_t)(threshold >> 32);
+    uint32_t out = m;
+    while (m) {
+        const int j = __clz(m);
+        m &= ~(0x80000000u >> j);
+        const int s = 62 - 2 * j;
+        uint32_t lo, hi;
+        if (s >= 32) { lo = __funnelshift_r(c2, c1, s - 32); hi = __funnelshift_r(c1, c0, s - 32); }
+        else { lo = __funnelshift_r(c3, c2, s); hi = __funnelshift_r(c2, c1, s); }
+        const uint64_t fw = (((uint64_t)hi << 32) | lo) & kmask;
+        uint64_t r = __brevll(~fw);                                     // reverse the bits ...
+        r = ((r >> 1) & 0x5555555555555555ull) | ((r & 0x5555555555555555ull) << 1);   // ... each base's two bits back in order
+        r >>= (64 - 2 * K);
+        const uint64_t can = fw < r ? fw : r;
+        if (!(fr_sample_hash((uint32_t)can, (uint32_t)(can >> 32), seedmix) < thr32)) out &= ~(0x80000000u >> j);
+    }
+    return out;
+}
+
+// CORE = true: first stage = core bitmap (any library), second stage = sampler test on the survivors when the
+// library is a verified sample.  CORE = false: the per-position filters above (one-bit filter probe per
+// position, or the sampler evaluated at every position) -- FR_EXTRACT_FILTER=old, for A/B measurements.
+template <bool WIDE, bool SAMPLED, bool CORE>
 __global__ void __launch_bounds__(FR_THREADS, 8)
 fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int64_t *__restrict__ offsets,
                   int64_t n_reads, FrTable tb, int32_t *scratch, int64_t scratch_cap, uint32_t *spill,
@@ -537,7 +600,7 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 }
                 sh.codes[w] = c;
                 sh.inv[w] = iv;
-                if (SAMPLED) {      // reverse the 2-bit groups and complement
+                if (SAMPLED && !CORE) {      // reverse the 2-bit groups and complement
                     uint32_t rv = __brev(c);
                     rv = ((rv >> 1) & 0x55555555u) | ((rv & 0x55555555u) << 1);
                     sh.rcodes[w] = ~rv;
@@ -558,7 +621,10 @@ fr_extract_kernel(const uint8_t *__restrict__ bases, int64_t n_bases, const int6
                 if (iv64) {
                     for (int d = 0; d < K; ++d) am |= (uint32_t)(iv64 >> d);
                 }
-                if (SAMPLED) {
+                if (CORE) {
+                    pass = fr_filter32_core(c0, c1, c2, c3, tb) & pm & ~am;
+                    if (SAMPLED && pass) pass = fr_refine_sampled(c0, c1, c2, c3, pass, K, kmask, tb.seed, tb.threshold);
+                } else if (SAMPLED) {
                     // reverse-complement stream of the same 64 positions, shifted right by 2*(33-K) bits
                     const uint32_t r0 = sh.rcodes[wi], r1 = sh.rcodes[wi + 1], r2 = sh.rcodes[wi + 2],
                                    r3 = sh.rcodes[wi + 3];
@@ -745,18 +811,21 @@ int fr_extract_launch(fr_ctx *ctx, const uint8_t *d_bases, int64_t n_bases, cons
     if (grid < 1) grid = 1;
     typedef void (*KernelFn)(const uint8_t *, int64_t, const int64_t *, int64_t, FrTable, int32_t *, int64_t, uint32_t *,
                              int64_t, int64_t *, int32_t *, unsigned long long *, const int32_t *, int);
-    static const KernelFn fns[4] = {fr_extract_kernel<false, false>, fr_extract_kernel<true, false>,
-                                    fr_extract_kernel<false, true>, fr_extract_kernel<true, true>};
+    static const KernelFn fns[8] = {fr_extract_kernel<false, false, false>, fr_extract_kernel<true, false, false>,
+                                    fr_extract_kernel<false, true, false>, fr_extract_kernel<true, true, false>,
+                                    fr_extract_kernel<false, false, true>, fr_extract_kernel<true, false, true>,
+                                    fr_extract_kernel<false, true, true>, fr_extract_kernel<true, true, true>};
     static bool attr_set = false;
     if (!attr_set) {
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 8; ++i)
             FR_CUDA(ctx, cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)sizeof(FrExtractShared)));
         attr_set = true;
     }
     static const int dbg = getenv("FR_EXTRACT_DEBUG") ? atoi(getenv("FR_EXTRACT_DEBUG")) : 0;   // timing experiments only
     // a k-mer of k <= 16 fits one 32-bit word; a verified sampled library skips the filter loads
-    const KernelFn fn = fns[(ctx->table.k > 16 ? 1 : 0) + (ctx->table.sampled && !(dbg & 8) ? 2 : 0)];
+    static const bool old_filter = getenv("FR_EXTRACT_FILTER") && !strcmp(getenv("FR_EXTRACT_FILTER"), "old");
+    const KernelFn fn = fns[(ctx->table.k > 16 ? 1 : 0) + (ctx->table.sampled && !(dbg & 8) ? 2 : 0) + (old_filter ? 0 : 4)];
     if (n_reads >= (1ll << 31)) return fr_fail(ctx, FR_ERR_ARG, "fr_extract: more than 2^31 reads in one call");
     if (n_reads > 0) {
         fr_kt_begin(ctx, "fr_read_order_kernel", st);

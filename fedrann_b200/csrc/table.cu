@@ -5,6 +5,7 @@
 // never on the hash function or insertion order.
 #include "common.cuh"
 
+#include <cmath>
 #include <cstdlib>
 
 __global__ void fr_table_insert_compact_kernel(const uint64_t *__restrict__ codes, int64_t n,
@@ -46,6 +47,20 @@ __global__ void fr_table_insert_kernel(const uint64_t *__restrict__ codes, int64
             return;
         }
         slot = (slot + 1) & cap_mask;
+    }
+}
+
+// core bitmap: every library k-mer sets the bits of its core_w cores (the c-mers at offsets 0 .. core_w - 1)
+__global__ void fr_table_cores_kernel(const uint64_t *__restrict__ codes, int64_t n, uint32_t *cores, int K, int w,
+                                      int c, int lg, int hashed) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t key = codes[i];
+    const uint64_t cmask = c >= 32 ? ~0ull : ((1ull << (2 * c)) - 1);
+    for (int o = 0; o < w; ++o) {
+        const uint64_t core = (key >> (2 * (K - c - o))) & cmask;
+        const uint32_t idx = fr_core_index(core, lg, hashed);
+        atomicOr(&cores[idx >> 5], 1u << (idx & 31));
     }
 }
 
@@ -107,6 +122,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     cudaStream_t st = (cudaStream_t)stream;
     FR_CUDA(ctx, cudaSetDevice(ctx->device));
     if (ctx->d_bloom) { cudaFree(ctx->d_bloom); ctx->d_bloom = nullptr; }
+    if (ctx->d_cores) { cudaFree(ctx->d_cores); ctx->d_cores = nullptr; }
     if (ctx->d_slots) { cudaFree(ctx->d_slots); ctx->d_slots = nullptr; }
     if (ctx->d_cslots) { cudaFree(ctx->d_cslots); ctx->d_cslots = nullptr; }
     ctx->has_table = false;
@@ -123,6 +139,36 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     if (cudaMalloc(&ctx->d_bloom, words * 4) != cudaSuccess ||
         (vbits ? cudaMalloc(&ctx->d_cslots, cap * 8) : cudaMalloc(&ctx->d_slots, cap * 16)) != cudaSuccess)
         return fr_fail(ctx, FR_ERR_NOMEM, "fr_table_build: cudaMalloc failed");
+    // core bitmap geometry: w positions share the (k - w + 1)-mer ending at the first of them.  A probe costs
+    // about a third of what a surviving position costs downstream (queue + table probe), so minimise
+    // 1/w + 3 * P(group passes), P = 1 - exp(-w n / bits); cores of <= 14 bases index the bitmap directly.
+    int core_w = 1, core_c = k, core_lg = 10, core_hashed = 0;
+    {
+        double best = 1e30;
+        for (int w = 1; w <= 8 && w <= k; w *= 2) {
+            const int c = k - w + 1;
+            const int lg_eff = 2 * c <= 28 ? 2 * c : 28;
+            const double p = 1.0 - exp(-(double)w * (double)(n > 0 ? n : 1) / ldexp(1.0, lg_eff));
+            const double cost = 1.0 / w + 3.0 * p;
+            if (cost < best) {
+                best = cost; core_w = w; core_c = c;
+                core_hashed = 2 * c > 28;
+                core_lg = lg_eff < 10 ? 10 : lg_eff;
+            }
+        }
+        if (const char *ov = getenv("FR_CORE_W")) {          // timing experiments only
+            const int w = atoi(ov);
+            if ((w == 1 || w == 2 || w == 4 || w == 8) && w <= k) {
+                core_w = w; core_c = k - core_w + 1;
+                core_hashed = 2 * core_c > 28;
+                core_lg = core_hashed ? 28 : (2 * core_c < 10 ? 10 : 2 * core_c);
+            }
+        }
+    }
+    const size_t core_words = ((size_t)1 << core_lg) / 32;
+    if (cudaMalloc(&ctx->d_cores, core_words * 4) != cudaSuccess)
+        return fr_fail(ctx, FR_ERR_NOMEM, "fr_table_build: cudaMalloc failed (core bitmap)");
+    FR_CUDA(ctx, cudaMemsetAsync(ctx->d_cores, 0, core_words * 4, st));
     if (vbits) FR_CUDA(ctx, cudaMemsetAsync(ctx->d_cslots, 0xFF, cap * 8, st));
     else FR_CUDA(ctx, cudaMemsetAsync(ctx->d_slots, 0xFF, cap * 16, st));
     FR_CUDA(ctx, cudaMemsetAsync(ctx->d_bloom, 0, words * 4, st));
@@ -137,7 +183,16 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
             fr_table_insert_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_slots, ctx->d_bloom,
                                                                           lg_cap, lg_words);
         FR_LAUNCH_CHECK(ctx, "fr_table_insert_kernel");
+        fr_kt_begin(ctx, "fr_table_cores_kernel", st);
+        fr_table_cores_kernel<<<(unsigned)blocks, threads, 0, st>>>(d_codes, n, ctx->d_cores, k, core_w, core_c, core_lg,
+                                                                   core_hashed);
+        FR_LAUNCH_CHECK(ctx, "fr_table_cores_kernel");
     }
+    ctx->table.cores = ctx->d_cores;
+    ctx->table.core_w = core_w;
+    ctx->table.core_c = core_c;
+    ctx->table.core_lg = core_lg;
+    ctx->table.core_hashed = core_hashed;
     ctx->table.cslots = ctx->d_cslots;
     ctx->table.vbits = vbits;
     ctx->table.bloom = ctx->d_bloom;

@@ -138,8 +138,50 @@ class HostBuffers:
         return 4 * self.nbr_idx.numel() + 4 * self.nbr_dist.numel()
 
 
+# planning constants of the host path's schedule (orders of magnitude are what matters): pinned host -> device copy
+# rate and the distance kernel's rate on this machine
+_H2D_BYTES_PER_S = 50e9
+_K6_FLOPS_PER_S = 1.0e15
+
+
+def phase_schedule(n_bases: int, n_rows: int, Dp: int):
+    """Where the host path cuts the reads: (chunk cuts, phase ends) as cumulative fractions of the bases.
+
+    The copy of the reads is LINEAR in the fraction f that has arrived (C * f), the distance work that can
+    be done with it QUADRATIC (W * f^2), so early on the GPU can only wait for PCIe and at the end the copy
+    is long over: whatever the schedule, the step cannot end before max_f (C f + W (1 - f^2)), reached at
+    f* = C / 2W.  The first search phase is therefore placed at f* (a small read set like the E. coli
+    configuration is copy-bound, f* ~ 0.8: few late phases; the chr1 scale is compute-bound, f* ~ 0.15:
+    start early), and every later phase where the copy will have got to by the time the previous phase's
+    work is done, at least 15 % further (every phase costs a pair of launches and a candidate buffer per
+    row).  Reads between phase ends are still copied / extracted / projected in pieces of <= 15 %."""
+    C = n_bases / _H2D_BYTES_PER_S
+    W = 2.0 * float(n_rows) * float(n_rows) * Dp / _K6_FLOPS_PER_S
+    if W <= 0 or C <= 0:
+        return [], [1.0]
+    p = min(0.6, max(0.1, C / (2.0 * W)))
+    ends, t_free, prev = [], 0.0, 0.0
+    while p < 0.999 and len(ends) < 6:
+        ends.append(p)
+        t_free = max(t_free, C * p) + W * (p * p - prev * prev)
+        prev = p
+        p = max(p + 0.15, min(1.0, t_free / C))
+        if p > 0.9:
+            break
+    ends.append(1.0)
+    cuts, last = [], 0.0
+    for e in ends:
+        n_extra = int((e - last - 1e-9) / 0.15)
+        for i in range(1, n_extra + 1):
+            cuts.append(last + (e - last) * i / (n_extra + 1))
+        if e < 1.0:
+            cuts.append(e)
+        last = e
+    return cuts, ends
+
+
 def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *, mode: int = 0, group=None,
-                      timers: StageTimes | None = None, chunks=(0.15, 0.3, 0.45, 0.6, 0.8), rows_per_rank=None,
+                      timers: StageTimes | None = None, chunks=None, rows_per_rank=None,
                       knn_overlap: bool = True, knn_phase_ends=None, async_extract: bool = True,
                       direct_out: bool = True, trace: list | None = None) -> HotPathResult:
     """The call a host program makes: reads in pinned host memory -> device ->
@@ -153,11 +195,14 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
     fr_knn_inc_*): after chunk c the new embedding rows are searched against all
     rows present and the earlier rows against the new ones, so only the last
     chunk's share of the distance work is left when the copy ends.
-    knn_phase_ends: the chunk counts after which a phase runs.  Default: the last two cuts and the
-    end -- every launch of the distance kernel costs ~0.1 ms of ramp and tail and the rows of a new
-    chunk start their thresholds from -inf on all CTAs at once, so early, small phases cost more
-    than they hide (scripts/e2e_tune.py: 9.3 ms without overlap, 8.8 ms with this schedule, 10.8 ms
-    with a phase after each of 8 equal chunks, c2 on one B200).
+    chunks / knn_phase_ends: where to cut the reads and after which chunk counts a search phase runs.
+    Default (both None): phase_schedule() above, from the size of the read set and of the distance work
+    (E. coli configuration: cuts at 15/30/45/60/.../89 %, phases after 60 / 78 / 100 % -- every launch of
+    the distance kernel costs ~0.1 ms of ramp and tail and the rows of a new chunk start their thresholds
+    from -inf on all CTAs at once, so early, small phases cost more than they hide there
+    (scripts/e2e_tune.py: 9.3 ms without overlap, 8.8 ms with phases after 60 / 80 / 100 %, 10.8 ms with a
+    phase after each of 8 equal chunks); chr1 scale: phases after ~15 / 30 / 52 / 100 %, which keeps the
+    GPU busy from the moment a sixth of the reads has arrived).
     async_extract: chunks go through fr_extract_async (room for one hit per 8 bases, no host
     synchronisation per chunk: the host queues the whole step and the GPU is only ever waiting for
     PCIe); a chunk that does not fit is reported at the end and the step is redone synchronously.
@@ -180,6 +225,9 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
     offsets_d = hb.offsets.to(dev, non_blocking=True)
     # read ranges by bases: `chunks` equal pieces, or the cumulative fractions given
     chunks_arg = chunks
+    auto_ends = None
+    if chunks is None:
+        chunks, auto_ends = phase_schedule(n, 2 * R, (P_dev[3] + 63) // 64 * 64)
     fracs = [c / chunks for c in range(1, chunks)] if isinstance(chunks, int) else [float(f) for f in chunks if 0 < f < 1]
     fracs = fracs[: max(0, R - 1)]
     off = hb.offsets
@@ -206,7 +254,12 @@ def run_hot_path_host(eng: Engine, hb: HostBuffers, P_dev, nk: int, k_nn: int, *
     k_eff = min(k_nn, 2 * R)
     inc = knn_overlap and mode == 0 and not multi and chunks > 1 and Engine.knn_inc_supported(2 * R, D, k_eff)
     if inc:
-        default_ends = range(max(1, chunks - 2), chunks + 1)
+        if auto_ends is not None and knn_phase_ends is None and len(fracs) == chunks - 1:
+            # phase ends as chunk counts: the chunk whose cut is the phase's fraction
+            default_ends = [1 + min(range(len(fracs)), key=lambda i: abs(fracs[i] - e)) if e < 1.0 and fracs else chunks
+                            for e in auto_ends]
+        else:
+            default_ends = range(max(1, chunks - 2), chunks + 1)
         ends = sorted(set(int(e) for e in (knn_phase_ends or default_ends) if 1 <= int(e) < chunks) | {chunks})
         ends = ends[-64:]                       # fr_knn_inc_begin takes at most 64 phases
         Dp = (D + 63) // 64 * 64
