@@ -213,7 +213,10 @@ class Workload:
         torch.cuda.empty_cache()
         self.n_reads_total, self.n_reads_local = R, self.r1 - self.r0
         codes, counts = SD.sampled_kmer_counts(self.bases, self.offsets, w["k"], w["fraction"], w["seed"])
-        codes, counts = SD.merge_counts(codes, counts)
+        if world > 1:       # N1 across ranks: hash-partitioned owners, one all-to-all (parallel.partitioned_kmer_counts)
+            import torch.distributed as dist
+            from fedrann_b200.parallel import partitioned_kmer_counts
+            codes, counts = partitioned_kmer_counts(codes, counts, w["min_mult"], dist.group.WORLD)
         self.lib = SD.library_from_counts(codes, counts, w["k"], w["min_mult"], w["seed"])
         del codes, counts
         torch.cuda.empty_cache()

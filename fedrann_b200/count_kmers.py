@@ -69,12 +69,13 @@ def sample_library(eng: Engine, bases_d: torch.Tensor, offsets_d: torch.Tensor, 
                                     min_multiplicity if world == 1 else 1)
     counts = counts.astype(np.uint64)
     if world > 1:
-        from .synthetic_device import merge_counts
-        c, n = merge_counts(torch.from_numpy(codes.view(np.int64)).to(bases_d.device),
-                            torch.from_numpy(counts.view(np.int64)).to(bases_d.device), group)
-        codes, counts = c.cpu().numpy().view(np.uint64), n.cpu().numpy().view(np.uint64)
-        keep = counts >= np.uint64(min_multiplicity)
-        codes, counts = codes[keep], counts[keep]
+        # hash-partitioned merge: one all-to-all of the partial counts to their owners, multiplicity cut there,
+        # all-gather of the (small) library
+        from .parallel import partitioned_kmer_counts
+        c, n = partitioned_kmer_counts(torch.from_numpy(codes.view(np.int64)).to(bases_d.device),
+                                       torch.from_numpy(counts.astype(np.int64)).to(bases_d.device),
+                                       min_multiplicity, group)
+        codes, counts = c.cpu().numpy().view(np.uint64), n.cpu().numpy().astype(np.uint64)
     # jellyfish dumps in its hash order; ours is a seeded hash order (deterministic)
     order = np.lexsort((codes, splitmix64(codes + np.uint64(seed & (2 ** 64 - 1)))))
     return codes[order], counts[order]
@@ -136,15 +137,17 @@ def run_kmer_searcher(input_path: str, k: int, sample_fraction: float, min_multi
     if world > 1:
         torch.distributed.all_reduce(docfreq, group=group)
     if write_files:
-        ip, ix = indptr.cpu().numpy(), indices.cpu().numpy()
         if world > 1:
-            parts = [None] * world
-            torch.distributed.all_gather_object(parts, (ip, ix), group=group)
+            # rows of every rank to rank 0, as tensors: per-read hit counts and the indices, in rank = input order
+            from .parallel import gather_to_rank0
+            cnt_all = gather_to_rank0(indptr[1:] - indptr[:-1], group)
+            ix_all = gather_to_rank0(indices, group)
             if rank == 0:
-                ips = [p[0] for p in parts]
-                ix = np.concatenate([p[1] for p in parts])
-                base = np.cumsum([0] + [int(a[-1]) for a in ips[:-1]])
-                ip = np.concatenate([ips[0][:1]] + [a[1:] + b for a, b in zip(ips, base)])
+                ip = np.zeros(cnt_all.numel() + 1, dtype=np.int64)
+                np.cumsum(cnt_all.cpu().numpy(), out=ip[1:])
+                ix = ix_all.cpu().numpy()
+        else:
+            ip, ix = indptr.cpu().numpy(), indices.cpu().numpy()
         if rank == 0:
             os.makedirs(out_dir, exist_ok=True)              # kmer_searcher.cpp:253-256
             write_output_bin(output_bin, reads.names, ip, ix)

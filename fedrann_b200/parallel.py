@@ -38,6 +38,87 @@ def shard_reads(offsets: np.ndarray, world: int) -> np.ndarray:
     return np.array([(R * r) // world for r in range(world + 1)], dtype=np.int64)
 
 
+def _all_to_all_rows(parts, group):
+    """parts[r] = int64 [n_r, 2] rows this rank sends to rank r -> list of the blocks received from every
+    rank.  NCCL: one size exchange + one all_to_all_single of the data.  gloo (CPU tests) has no
+    all-to-all: the blocks travel through all_gather_object there."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if parts[0].is_cuda:
+        dev = parts[0].device
+        send_n = torch.tensor([p.shape[0] for p in parts], dtype=torch.int64, device=dev)
+        recv_n = torch.empty(world, dtype=torch.int64, device=dev)
+        dist.all_to_all_single(recv_n, send_n, group=group)
+        recv_counts = [int(x) for x in recv_n.cpu()]
+        send = torch.cat(parts).contiguous()
+        recv = torch.empty((sum(recv_counts), 2), dtype=torch.int64, device=dev)
+        dist.all_to_all_single(recv, send, output_split_sizes=recv_counts,
+                               input_split_sizes=[p.shape[0] for p in parts], group=group)
+        return list(recv.split(recv_counts, dim=0))
+    everything = [None] * world
+    dist.all_gather_object(everything, [p.numpy() for p in parts], group=group)
+    return [torch.from_numpy(everything[r][rank]) for r in range(world)]
+
+
+def partitioned_kmer_counts(codes: torch.Tensor, counts: torch.Tensor, min_multiplicity: int, group=None):
+    """The multi-GPU half of N1 ("hash-partitioned across GPUs with one all-to-all"; replaces the
+    single jellyfish table of fedrann/count_kmers.py:76-123).  Every rank has counted the sampled canonical
+    k-mers of ITS reads (codes int64, counts int64, any order).  Rank hash(code) % world owns a k-mer: one
+    all-to-all sends every (code, count) pair to its owner, the owner sums the partial counts and applies the
+    multiplicity cut, and the survivors -- the library, a small fraction of what was counted -- are all-gathered.
+    -> (codes int64 ascending, counts int64), identical on every rank."""
+    world = dist.get_world_size(group) if group is not None else 1
+    if world == 1:
+        keep = counts >= min_multiplicity
+        c, n = codes[keep], counts[keep]
+        order = torch.argsort(c)
+        return c[order], n[order]
+    from .synthetic_device import splitmix64_t
+    owner = (splitmix64_t(codes) & 0x7FFFFFFFFFFFFFFF) % world
+    order = torch.argsort(owner, stable=True)
+    pairs = torch.stack([codes[order], counts[order]], dim=1)
+    sizes = torch.bincount(owner, minlength=world).cpu().tolist()
+    got = _all_to_all_rows(list(pairs.split(sizes, dim=0)), group)
+    mine = torch.cat(got) if got else pairs[:0]
+    u, inv = torch.unique(mine[:, 0], return_inverse=True)
+    tot = torch.zeros_like(u).scatter_add_(0, inv, mine[:, 1])
+    keep = tot >= min_multiplicity
+    u, tot = u[keep], tot[keep]
+    # the library: every rank needs all of it
+    n_mine = torch.tensor([u.numel()], dtype=torch.int64, device=u.device)
+    ns = [torch.zeros_like(n_mine) for _ in range(world)]
+    dist.all_gather(ns, n_mine, group=group)
+    ns = [int(x) for x in ns]
+    nmax = max(max(ns), 1)
+    pad = torch.zeros((nmax, 2), dtype=torch.int64, device=u.device)
+    pad[: u.numel(), 0], pad[: u.numel(), 1] = u, tot
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad, group=group)
+    lib = torch.cat([out[r][: ns[r]] for r in range(world)])
+    order = torch.argsort(lib[:, 0])
+    return lib[order, 0].contiguous(), lib[order, 1].contiguous()
+
+
+def gather_to_rank0(x: torch.Tensor, group=None):
+    """1-D tensors of different lengths -> their concatenation in rank order on rank 0 (None elsewhere);
+    tensors travel as tensors (NCCL gather of padded buffers), not as pickled objects."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    n = torch.tensor([x.numel()], dtype=torch.int64, device=x.device)
+    ns = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(ns, n, group=group)
+    ns = [int(v) for v in ns]
+    nmax = max(max(ns), 1)
+    pad = torch.zeros(nmax, dtype=x.dtype, device=x.device)
+    pad[: x.numel()] = x
+    dst = dist.get_global_rank(group, 0) if group is not None and group is not dist.group.WORLD else 0
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == 0 else None
+    dist.gather(pad, bufs, dst=dst, group=group)
+    if rank != 0:
+        return None
+    return torch.cat([bufs[r][: ns[r]] for r in range(world)])
+
+
 class _DeviceArray:
     """CUDA array interface over memory the native library owns (the exchange slab)."""
 

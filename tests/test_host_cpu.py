@@ -77,3 +77,42 @@ def test_all_gather_rows_world2_gloo():
     assert A0 == A1 and C0 == C1 and len(A0) == 13
     assert q00 == 0 and q01 == 5
     assert C0[:5] == [0, 1, 2, 3, 4] and C0[5:] == [100 + i for i in range(8)]
+
+
+def _gloo_count_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from fedrann_b200.parallel import init_from_env, partitioned_kmer_counts, gather_to_rank0
+    init_from_env("gloo")
+    rng = np.random.default_rng(100 + rank)
+    # every rank counted some k-mers of its own reads; many k-mers are seen by both ranks
+    codes = np.unique(rng.integers(0, 4000, 1500 + 200 * rank)).astype(np.int64)
+    counts = rng.integers(1, 4, len(codes)).astype(np.int64)
+    c, n = partitioned_kmer_counts(torch.from_numpy(codes), torch.from_numpy(counts), 3, dist.group.WORLD)
+    g = gather_to_rank0(torch.arange(3 + 2 * rank, dtype=torch.int32) + 10 * rank, dist.group.WORLD)
+    q.put((rank, codes.tolist(), counts.tolist(), c.tolist(), n.tolist(), None if g is None else g.tolist()))
+    dist.destroy_process_group()
+
+
+def test_partitioned_kmer_counts_world2_gloo():
+    """N1 across ranks: hash-partitioned owners, one all-to-all, multiplicity cut at the owner, library
+    all-gathered -- same (codes, counts) on every rank as summing everything in one place."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    ps = [ctx.Process(target=_gloo_count_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=180) for _ in range(2))
+    [p.join(60) for p in ps]
+    total = {}
+    for _, codes, counts, _, _, _ in res:
+        for c, n in zip(codes, counts):
+            total[c] = total.get(c, 0) + n
+    want = sorted((c, n) for c, n in total.items() if n >= 3)
+    for _, _, _, c, n, _ in res:
+        assert list(zip(c, n)) == want
+    assert res[0][5] == [0, 1, 2, 10, 11, 12, 13, 14] and res[1][5] is None
