@@ -143,16 +143,22 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     // about a third of what a surviving position costs downstream (queue + table probe), so minimise
     // 1/w + 3 * P(group passes), P = 1 - exp(-w n / bits); cores of <= 14 bases index the bitmap directly.
     int core_w = 1, core_c = k, core_lg = 10, core_hashed = 0;
+    // bitmap of at most 2^LGMAX bits: 16 MB by default -- a 32 MB bitmap next to the 32 MB table and the
+    // streamed reads no longer stays L2-resident (measured: its probes ran at half the rate, profiles/r02d_*)
+    int LGMAX = 27;
+    if (const char *ov = getenv("FR_CORE_LG")) LGMAX = atoi(ov);      // timing experiments only
+    if (LGMAX < 16) LGMAX = 16;
+    if (LGMAX > 30) LGMAX = 30;
     {
         double best = 1e30;
         for (int w = 1; w <= 8 && w <= k; w *= 2) {
             const int c = k - w + 1;
-            const int lg_eff = 2 * c <= 28 ? 2 * c : 28;
+            const int lg_eff = 2 * c <= LGMAX ? 2 * c : LGMAX;
             const double p = 1.0 - exp(-(double)w * (double)(n > 0 ? n : 1) / ldexp(1.0, lg_eff));
             const double cost = 1.0 / w + 3.0 * p;
             if (cost < best) {
                 best = cost; core_w = w; core_c = c;
-                core_hashed = 2 * c > 28;
+                core_hashed = 2 * c > LGMAX;
                 core_lg = lg_eff < 10 ? 10 : lg_eff;
             }
         }
@@ -160,8 +166,8 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
             const int w = atoi(ov);
             if ((w == 1 || w == 2 || w == 4 || w == 8) && w <= k) {
                 core_w = w; core_c = k - core_w + 1;
-                core_hashed = 2 * core_c > 28;
-                core_lg = core_hashed ? 28 : (2 * core_c < 10 ? 10 : 2 * core_c);
+                core_hashed = 2 * core_c > LGMAX;
+                core_lg = core_hashed ? LGMAX : (2 * core_c < 10 ? 10 : 2 * core_c);
             }
         }
     }
