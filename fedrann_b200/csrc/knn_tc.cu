@@ -570,19 +570,16 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
         }
     } else {
         // ------------------------------------------------ epilogue: threshold filter + candidate buffers
-        // TC_EPQ warps share each TMEM lane quadrant (32 query rows): they take alternate 16-column chunks
-        // of every tile.  Every warp has candidate buffers OF ITS OWN for its 32 rows (like two CTAs that
-        // share the rows): it appends at a position it keeps in a register and compacts a buffer that
-        // could overflow during the next tile by itself, so the warps of a quadrant never wait for each
-        // other inside a segment (round 1 shared one buffer per row: two named barriers per tile, 10-20 %
-        // of the epilogue).  What they do share is the row's threshold, a shared-memory word raised with
-        // atomicMax: a threshold reached by either warp (it keeps >= klo candidates at or above it) is
-        // valid for the row, exactly as between CTAs.
+        // TC_EPQ warps share each TMEM lane quadrant (32 query rows): they take alternate 16-column
+        // chunks of every tile, append through a shared-memory counter per row, and compact full
+        // buffers between tiles (rows split among the quadrant's warps).
         const int quad = warp & 3;                       // TMEM lanes 32*quad .. 32*quad+31
         const int sub = (warp - 2) >> 2;                 // which of the quadrant's warps
         const int row_in_tile = quad * 32 + lane;
-        unsigned int *s_thr = reinterpret_cast<unsigned int *>(gbase + (sRow - base));   // orderable floats, 0 = none yet
+        float *s_thr = reinterpret_cast<float *>(gbase + (sRow - base));
+        int *s_cnt = reinterpret_cast<int *>(s_thr + TC_M);      // [TC_EPQ][TC_M]: entries appended by each warp
         const int bar_id = 1 + quad;
+        const int step = sub ? -1 : 1;
         uint32_t tile = 0;
         // "accumulator drained" is counted where the MMA issuer waits: the leader's barrier for a pair
         const uint32_t rTEmpty = PAIR ? mapa_u32(bTEmpty, 0) : bTEmpty;
@@ -594,13 +591,21 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
             const int64_t grow = qt * TC_M + row_in_tile;
             const bool valid = grow < p.nq && p.norms[p.q0 + grow] > 0.0f;
             const int64_t wrow = valid ? grow + p.ws_off : 0;          // this row in the workspace
-            const int64_t stream = (wrow * p.slots + p.slot_base + slot) * TC_EPQ + sub;
+            const int64_t stream = wrow * p.slots + p.slot_base + slot;
             unsigned long long *buf = p.keys + stream * CAP;
+            unsigned long long *ptr = sub ? buf + CAP - 1 : buf;     // this warp's end of the row's buffer
             int mycnt = 0;
             bool sparse_next = false;
             const uint32_t allow = valid ? 0xFFFFu : 0u;
-            if (sub == 0)      // start from whatever the row's other CTAs (or this CTA's earlier segment) reached
-                s_thr[row_in_tile] = valid ? __ldcg(p.gthr + wrow) : f2ord(INFINITY);
+            if (sub == 0) {
+                // start from whatever the row's other CTAs (or this CTA's earlier segment) reached
+                float t0v = INFINITY;
+                if (valid) {
+                    const unsigned int g = __ldcg(p.gthr + wrow);
+                    t0v = g ? ord2f(g) : -INFINITY;
+                }
+                s_thr[row_in_tile] = t0v;
+            }
             tc_quad_bar(bar_id);
             const int64_t len = t1 - t0, rot = ((int64_t)tile + p.rot_base) % len;   // the producer's order (tile = tiles done)
             for (int64_t i = 0; i < len; ++i, ++tile) {
@@ -608,9 +613,9 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                 const uint32_t ab = tile & 1;
                 mbar_wait_t(bTFull + 8 * ab, (tile >> 1) & 1, w0, dbg_on);
                 tc_fence_after();
-                const unsigned int su = *reinterpret_cast<volatile unsigned int *>(s_thr + row_in_tile);
-                const float thr = su ? ord2f(su) : -INFINITY;
-                // the row's global threshold (other CTAs) is requested now and looked at after the tile's filter
+                const float thr = s_thr[row_in_tile];
+                // the row's shared threshold is requested now and looked at after the tile's filter: an
+                // L2 round trip between the two tile barriers would stall both warps of the quadrant
                 unsigned int g_seen = 0;
                 if (sub == 0 && valid) g_seen = __ldcg(p.gthr + wrow);
                 const uint32_t taddr = tmem + ((uint32_t)(quad * 32) << 16) + ab * TC_N;
@@ -632,7 +637,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     tc_ld16(taddr + (c + 4) * TC_CH, b0);
                     tc_ld16(taddr + (c + 6) * TC_CH, b1);
                     tc_filter_pair(a0, a1, (uint32_t)(col0 + c * TC_CH), (uint32_t)(col0 + (c + 2) * TC_CH), ragged,
-                                       p.db_end, buf, 1, mycnt, thr, allow, sparse);
+                                       p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) { const long long t2 = clock64(); e_flt += t2 - tq; tq = t2; }
                     tc_ld_wait();                                          // b0, b1 landed
                     if (dbg_on) { const long long t2 = clock64(); e_ld += t2 - tq; tq = t2; }
@@ -641,56 +646,67 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                         tc_ld16(taddr + (c + 10) * TC_CH, a1);
                     }
                     tc_filter_pair(b0, b1, (uint32_t)(col0 + (c + 4) * TC_CH), (uint32_t)(col0 + (c + 6) * TC_CH),
-                                       ragged, p.db_end, buf, 1, mycnt, thr, allow, sparse);
+                                       ragged, p.db_end, ptr, step, mycnt, thr, allow, sparse);
                     if (dbg_on) e_flt += clock64() - tq;
                 }
                 long long tb = dbg_on ? clock64() : 0;
                 tc_fence_before();
-                const int dh = mycnt - cnt_at_tile_start;
                 if (dbg_on) {       // hits of this tile: total and the warp's largest per-lane count
+                    const int dh = mycnt - cnt_at_tile_start;
                     n_hits += __reduce_add_sync(0xFFFFFFFFu, dh);
                     n_hitmax += __reduce_max_sync(0xFFFFFFFFu, dh);
                 }
-                // the next tile takes the max-first filter when this one had at most one hit per chunk
-                sparse_next = __reduce_add_sync(0xFFFFFFFFu, dh) <= TC_N / TC_CH / TC_EPQ;
+                // the next tile takes the max-first filter when this one had at most a hit per chunk
+                sparse_next = __reduce_add_sync(0xFFFFFFFFu, mycnt - cnt_at_tile_start) <= TC_N / TC_CH / TC_EPQ;
+                s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
                 if (lane == 0) {
                     if (PAIR) mbar_arrive_cluster(rTEmpty + 8 * ab);
                     else mbar_arrive(bTEmpty + 8 * ab);
                 }
+                tc_quad_bar(bar_id);                     // every append of this tile and both counts are visible
                 if (dbg_on) { const long long t2 = clock64(); e_bar += t2 - tb; tb = t2; }
+                // a buffer that could overflow during the next tile is compacted now
+                const int c0r = s_cnt[row_in_tile], c1r = s_cnt[TC_M + row_in_tile];
+                unsigned need = __ballot_sync(0xFFFFFFFFu, c0r + c1r > CAP - TC_N);
                 // A threshold reached by ANY CTA working on this query row is valid for all of them:
                 // that CTA keeps >= klo candidates at or above it.  Adopting it spares the CTAs that
                 // joined the row late (several slots per query tile: multi-GPU, small query sets)
-                // the slow climb from -inf.  The threshold only ever rises (it bounds everything dropped).
-                if (sub == 0 && valid && g_seen) atomicMax(s_thr + row_in_tile, g_seen);
-                // a buffer of this warp that could overflow during the next tile (128 of its columns) is compacted now
-                unsigned need = __ballot_sync(0xFFFFFFFFu, mycnt > CAP - TC_N / TC_EPQ);
+                // the slow climb from -inf.  s_thr only ever rises (it bounds everything dropped).
+                if (sub == 0 && valid && g_seen) {
+                    const float gt = ord2f(g_seen);
+                    if (gt > s_thr[row_in_tile]) s_thr[row_in_tile] = gt;
+                }
+                tc_quad_bar(bar_id);                     // both warps hold the same counts before either rewrites them
                 if (need) {
-                    while (need) {
-                        const int src = __ffs(need) - 1;
-                        need &= need - 1;
-                        const int n0 = __shfl_sync(0xFFFFFFFFu, mycnt, src);
+                    unsigned mine = need;
+                    while (mine) {
+                        const int src = __ffs(mine) - 1;
+                        mine &= mine - 1;
+                        if (src % TC_EPQ != sub) continue;   // the quadrant's other warp takes this row
+                        const int n0 = __shfl_sync(0xFFFFFFFFu, c0r, src), n1 = __shfl_sync(0xFFFFFFFFu, c1r, src);
                         const unsigned long long bp = __shfl_sync(0xFFFFFFFFu, (unsigned long long)buf, src);
                         int kept;
-                        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n0, 0,
+                        const float nt = tc_warp_select<CAP / 32>(reinterpret_cast<unsigned long long *>(bp), n0, n1,
                                                                   p.klo, p.khi, &kept);
                         if (lane == src) {
-                            atomicMax(s_thr + row_in_tile, f2ord(nt));
+                            if (nt > s_thr[row_in_tile]) s_thr[row_in_tile] = nt;
                             atomicMax(p.gthr + wrow, f2ord(nt));
-                            mycnt = kept;
+                            s_cnt[row_in_tile] = kept;
+                            s_cnt[TC_M + row_in_tile] = 0;
                         }
                         if (dbg_on && lane == 0) ++n_cmp;
                     }
-                    if (dbg_on) e_cmp += clock64() - tb;
+                    if (dbg_on) { const long long t2 = clock64(); e_cmp += t2 - tb; tb = t2; }
+                    tc_quad_bar(bar_id);                 // new thresholds / counts are visible
+                    mycnt = s_cnt[sub * TC_M + row_in_tile];
+                    if (dbg_on) e_bar += clock64() - tb;
                 }
             }
-            if (valid) {
-                // everything this warp dropped scored <= the threshold it filtered with, which never exceeded
-                // the row's current shared value
-                const unsigned int sf = *reinterpret_cast<volatile unsigned int *>(s_thr + row_in_tile);
-                p.counts[stream] = mycnt;
-                p.thrs[stream] = sf ? ord2f(sf) : -INFINITY;
+            if (sub == 0 && valid) {
+                // [15:0] keys at the front of the buffer, [31:16] keys at its end
+                p.counts[stream] = s_cnt[row_in_tile] | (s_cnt[TC_M + row_in_tile] << 16);
+                p.thrs[stream] = s_thr[row_in_tile];
             }
             tc_quad_bar(bar_id);                         // the next segment resets the row state
             u += t1 - t0;
@@ -1030,7 +1046,7 @@ int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, in
     p.norms = d_norms;
 
     // workspace: keys | counts | thrs | fallback rows | shared thresholds | fallback counter
-    const int64_t streams = ws_rows * slots * TC_EPQ;      // every epilogue warp of a quadrant has its own buffer
+    const int64_t streams = ws_rows * slots;
     const size_t keys_b = (size_t)streams * S.cap * 8, cnt_b = ((size_t)streams * 4 + 15) & ~(size_t)15;
     const size_t rows_b = ((size_t)ws_rows * 4 + 15) & ~(size_t)15;
     const size_t need = keys_b + 2 * cnt_b + 2 * rows_b + 16;
@@ -1103,8 +1119,7 @@ int tc_finish(fr_ctx *ctx, const TcSetup &S, const float *d_En, const float *d_n
     }
     // keys of one row K7 merges in shared memory (after dropping those below the shared threshold);
     // rows with more go to the exact paths.  The bound sets K7's occupancy: 8 bytes per key and warp.
-    const int bufs = p.slots * TC_EPQ;          // candidate buffers per row
-    int max_n = bufs * S.cap;
+    int max_n = p.slots * S.cap;
     if (max_n > max_keys) max_n = max_keys;
     const size_t rsmem = (size_t)RR_WARPS * ((size_t)max_n * 8 + (size_t)RR_RES * 8);
     FR_CUDA(ctx, cudaFuncSetAttribute(fr_knn_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
@@ -1112,7 +1127,7 @@ int tc_finish(fr_ctx *ctx, const TcSetup &S, const float *d_En, const float *d_n
     if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
     fr_kt_begin(ctx, "fr_knn_rerank_kernel", st);
     fr_knn_rerank_kernel<<<(unsigned)blocks, RR_WARPS * 32, rsmem, st>>>(
-        d_En, d_norms, p.n_db, D, q0, nq, k, bufs, S.cap, max_n, p.keys, p.counts, p.thrs, p.gthr, d_idx, d_dist,
+        d_En, d_norms, p.n_db, D, q0, nq, k, p.slots, S.cap, max_n, p.keys, p.counts, p.thrs, p.gthr, d_idx, d_dist,
         S.fb_rows, S.fb_count);
     FR_LAUNCH_CHECK(ctx, "fr_knn_rerank_kernel");
     // rows the certificate rejected: exact scan (reads the row list and its length on the device)

@@ -145,7 +145,7 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     int core_w = 1, core_c = k, core_lg = 10, core_hashed = 0;
     // bitmap of at most 2^LGMAX bits: 16 MB by default -- a 32 MB bitmap next to the 32 MB table and the
     // streamed reads no longer stays L2-resident (measured: its probes ran at half the rate, profiles/r02d_*)
-    int LGMAX = 27;
+    int LGMAX = 28;
     if (const char *ov = getenv("FR_CORE_LG")) LGMAX = atoi(ov);      // timing experiments only
     if (LGMAX < 16) LGMAX = 16;
     if (LGMAX > 30) LGMAX = 30;
