@@ -400,8 +400,13 @@ __device__ __forceinline__ void tc_filter_pair(const uint32_t (&va)[16], const u
                                                uint32_t cbase_b, bool ragged, int64_t n_db, unsigned long long *ptr,
                                                int step, int &pos, float thr, uint32_t allow, bool sparse) {
     if (sparse) {
-        const float mx = fmaxf(tc_max16(va), tc_max16(vb));
-        if (!(mx > thr) || !allow) return;
+        // the masks are built per chunk, and only for a chunk in which some lane of the warp has a hit: with
+        // about one hit per pair of chunks and warp, one of the two mask computations is skipped
+        const float ma = tc_max16(va), mb = tc_max16(vb);
+        if (!(fmaxf(ma, mb) > thr) || !allow) return;
+        if (ma > thr) tc_walk16(va, tc_mask16(va, cbase_a, ragged, n_db, thr, allow), cbase_a, ptr, step, pos);
+        if (mb > thr) tc_walk16(vb, tc_mask16(vb, cbase_b, ragged, n_db, thr, allow), cbase_b, ptr, step, pos);
+        return;
     }
     // one chunk at a time (building both masks first costs registers where hits are frequent: c2 +6 %)
     tc_walk16(va, tc_mask16(va, cbase_a, ragged, n_db, thr, allow), cbase_a, ptr, step, pos);
@@ -418,7 +423,9 @@ __device__ __forceinline__ void tc_filter_pair(const uint32_t (&va)[16], const u
 // Barriers of a pair: `full` / `a_full` / `tmem_empty` live in the LEADER (the CTA that issues the MMAs
 // waits on them; the peer's TMA completions and arrivals go there through shared::cluster addresses),
 // `empty` / `a_empty` / `tmem_full` exist in both CTAs and are signalled by multicast commits.
-template <int CAP, bool PAIR>
+// DBG = true (FR_KNN_DEBUG=1) compiles the per-role cycle counters in; the production instantiation carries none
+// of them (as a run-time flag they cost ~190 M predicated clock reads per 10 ms of kernel, ncu source view).
+template <int CAP, bool PAIR, bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     extern __shared__ unsigned char tc_smem_raw[];
@@ -464,7 +471,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
     const uint32_t tmem = *tmem_slot;
 
     const int cta = blockIdx.x / G;      // worker: a CTA, or a CTA pair
-    const bool dbg_on = p.dbg != nullptr;
+    constexpr bool dbg_on = DBG;
     long long w0 = 0, w1 = 0, e_ld = 0, e_flt = 0, e_bar = 0, e_cmp = 0, n_cmp = 0, n_hits = 0, n_hitmax = 0;
     const long long t_start = clock64();
     const int64_t u_begin = ((int64_t)cta * p.units) / p.n_ctas;
@@ -1075,10 +1082,21 @@ int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, in
 }
 
 // one K6 launch: query rows [q0, q0 + nq) against database rows [db0, db_end); p carries the geometry
+template <int CAP, bool PAIR, bool DBG>
+int tc_launch_k6_inst(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st);
+
 template <int CAP>
 int tc_launch_k6_cap(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st) {
-    if (p.pair) {
-        auto kern = fr_knn_tc_kernel<CAP, true>;
+    if (p.pair && p.dbg) return tc_launch_k6_inst<CAP, true, true>(ctx, S, p, st);
+    if (p.pair) return tc_launch_k6_inst<CAP, true, false>(ctx, S, p, st);
+    if (p.dbg) return tc_launch_k6_inst<CAP, false, true>(ctx, S, p, st);
+    return tc_launch_k6_inst<CAP, false, false>(ctx, S, p, st);
+}
+
+template <int CAP, bool PAIR, bool DBG>
+int tc_launch_k6_inst(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStream_t st) {
+    if (PAIR) {
+        auto kern = fr_knn_tc_kernel<CAP, true, DBG>;
         FR_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(2 * p.n_ctas));
@@ -1094,7 +1112,7 @@ int tc_launch_k6_cap(fr_ctx *ctx, const TcSetup &S, const TcParams &p, cudaStrea
         cfg.numAttrs = 1;
         FR_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, S.tmap, p));
     } else {
-        auto kern = fr_knn_tc_kernel<CAP, false>;
+        auto kern = fr_knn_tc_kernel<CAP, false, DBG>;
         FR_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
         kern<<<p.n_ctas, TC_THREADS, S.smem, st>>>(S.tmap, p);
     }
