@@ -603,6 +603,7 @@ def main():
                 "cpu_baseline": cpu, "stage_ms": stage_ms,
                 "kernels_ms_per_step": {k: v[1] / args.steps for k, v in ktimes.items()},
                 "knn_fallback_rows": {"device_path_last_step": fb_device, "e2e_path_last_step": fb_e2e},
+                "exchange": exchange_info(eng, world),
                 "workload_stats": {"n_features": wl.lib.n_features, "reads_this_rank": wl.n_reads_local,
                                    "bases_this_rank": int(wl.bases.numel()), "nnz_this_rank": int(res.indices.numel())}}
         if parity is not None:
@@ -615,6 +616,19 @@ def main():
 
 
 # ---------------------------------------------------------------------------
+def exchange_info(eng, world):
+    """How the ranks' embedding rows reached each other in this run (None on one GPU)."""
+    if world == 1:
+        return None
+    from fedrann_b200.pipeline import EXCHANGE
+    x = getattr(eng, "_row_exchange", None)
+    if EXCHANGE == "peer" and x:
+        return {"transport": "peer memory over NVLink (CUDA IPC slabs, copy-engine pulls in ring order, shard flags "
+                             "consumed by the distance kernel; csrc/exchange.cu)",
+                "bytes_pulled_per_rank_per_step": int(x[1].bytes_pulled_per_step)}
+    return {"transport": "nccl all_gather_into_tensor x3"}
+
+
 def gather_rows_rank0(x, counts, rank, world, group):
     """Row shards of every rank -> all rows in global order (valid on every rank)."""
     import torch
