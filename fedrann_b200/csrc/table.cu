@@ -143,8 +143,8 @@ extern "C" int fr_table_build(fr_ctx *ctx, const uint64_t *d_codes, int64_t n, i
     // about a third of what a surviving position costs downstream (queue + table probe), so minimise
     // 1/w + 3 * P(group passes), P = 1 - exp(-w n / bits); cores of <= 14 bases index the bitmap directly.
     int core_w = 1, core_c = k, core_lg = 10, core_hashed = 0;
-    // bitmap of at most 2^LGMAX bits: 16 MB by default -- a 32 MB bitmap next to the 32 MB table and the
-    // streamed reads no longer stays L2-resident (measured: its probes ran at half the rate, profiles/r02d_*)
+    // bitmap of at most 2^LGMAX bits (32 MB): cores of <= 14 bases index it directly.  Smaller caps (hashed
+    // 16 / 8 MB bitmaps) measured the same within noise (profiles/r02f_bench_c2_corelg*.json)
     int LGMAX = 28;
     if (const char *ov = getenv("FR_CORE_LG")) LGMAX = atoi(ov);      // timing experiments only
     if (LGMAX < 16) LGMAX = 16;

@@ -116,3 +116,21 @@ def test_partitioned_kmer_counts_world2_gloo():
     for _, _, _, c, n, _ in res:
         assert list(zip(c, n)) == want
     assert res[0][5] == [0, 1, 2, 10, 11, 12, 13, 14] and res[1][5] is None
+
+
+def test_phase_schedule_of_the_host_path():
+    """pipeline.phase_schedule: first search phase at f* = C / 2W (copy-bound read sets start late, compute-bound
+    ones early), later phases where the copy will have got to, pieces of at most 15 % in between."""
+    from fedrann_b200.pipeline import phase_schedule
+    for n_bases, n_rows, Dp in [(249e6, 50_000, 512), (7.4e9, 992_000, 256), (60e6, 12_000, 512), (1e6, 400, 64),
+                                (45e9, 6_000_000, 256), (1, 2, 64)]:
+        cuts, ends = phase_schedule(n_bases, n_rows, Dp)
+        assert ends[-1] == 1.0 and all(0 < a < b for a, b in zip(ends, ends[1:])) and len(ends) <= 7
+        assert all(0 < c < 1 for c in cuts) and cuts == sorted(cuts)
+        pts = [0.0] + cuts + [1.0]
+        assert max(b - a for a, b in zip(pts, pts[1:])) <= 0.15 + 1e-9
+        assert all(any(abs(e - c) < 1e-12 for c in cuts) for e in ends[:-1])     # every phase end is a cut
+    _, c2 = phase_schedule(249e6, 50_000, 512)
+    assert c2[0] == 0.6 and len(c2) == 3                      # copy-bound: what round 1 had tuned by hand
+    _, c3 = phase_schedule(7.4e9, 992_000, 256)
+    assert c3[0] < 0.2 and len(c3) >= 4                       # compute-bound: start a sixth into the copy
