@@ -407,6 +407,16 @@ def reference_arm(args):
 _REAL_STDOUT = None
 
 
+_T0 = time.perf_counter()
+
+
+def progress(msg: str) -> None:
+    """One line per phase on stderr (with the seconds since start): a run that stalls says where."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        sys.stderr.write("[bench %7.1fs] %s\n" % (time.perf_counter() - _T0, msg))
+        sys.stderr.flush()
+
+
 def emit(line: dict) -> None:
     """The ONE JSON line goes to the real stdout; everything else a native library prints there
     (NCCL's version banner) was redirected to stderr at start-up."""
@@ -449,8 +459,10 @@ def main():
 
     w = WORKLOADS[args.workload]
     group = dist.group.WORLD if world > 1 else None
+    progress("building workload %s on %d rank(s)" % (args.workload, world))
     wl = Workload(args.workload, rank, world, dev)
     assert wl.n_reads_total == config["reads"]
+    progress("workload ready: %d reads on this rank, %d features" % (wl.n_reads_local, wl.lib.n_features))
     eng = Engine(local)
     # the library is a hash-threshold sample (what N1 produces): declared to the engine, which verifies it
     eng.build_table(wl.lib.all_codes(), w["k"], sampler=(w["seed"], w["fraction"]))
@@ -484,9 +496,14 @@ def main():
         return [a.elapsed_time(b) for a, b in evs]
 
     n_warm = max(args.warmup, 3)
-    for _ in range(n_warm):
+    progress("table and projection uploaded; warm-up")
+    for i in range(n_warm):
         res = device_step()
+        if i == 0:
+            torch.cuda.synchronize()
+            progress("first step done")
     sync_all()
+    progress("warm-up done; timing %d steps" % args.steps)
     clocks = ClockSampler(physical_gpu_index(local))
     l0 = eng.launches
     eng.profile(True)
@@ -510,12 +527,14 @@ def main():
     value = wl.n_reads_total / (ms_per_step / 1e3)
     res = device_step()
     torch.cuda.synchronize()
+    progress("device-resident steps done: %.2f ms per step" % ms_per_step)
 
     # ---- the run proves its own answer (untimed)
     parity = None
     if not args.no_parity:
         parity = parity_block(args, w, wl, eng, res, rank, world, group, dev)
 
+    progress("parity block done" if parity is not None else "parity block skipped")
     # ---- e2e: pinned host buffers -> public API -> pinned host results
     e2e = None
     fb_e2e = None
@@ -548,6 +567,7 @@ def main():
             parity["parity_ok"] = bool(parity["parity_ok"] and flag.item())
         del hb
 
+    progress("host-path steps done")
     # ---- roofline of the dominant kernel (largest share of the device-timed step on this rank)
     peaks = measured_peaks()
     roof = roofline(ktimes, args.steps, wl, res, w, world, peaks, args.ncu_traffic, ms_per_step)
@@ -582,6 +602,7 @@ def main():
     except Exception as e:      # noqa: BLE001
         stage_roofs["fr_extract_kernel_generic"] = {"error": repr(e)}
 
+    progress("rooflines done")
     # ---- CPU baseline (rank 0, N=1 only): same host code as the reference arm, on this run's library
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
