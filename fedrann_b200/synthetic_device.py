@@ -269,31 +269,6 @@ def sampled_kmer_counts(bases: torch.Tensor, offsets: np.ndarray, k: int, fracti
     return torch.unique(allc, return_counts=True)
 
 
-def merge_counts(codes: torch.Tensor, counts: torch.Tensor, group=None):
-    """Sum per-rank (codes, counts) tables over a process group (the k-mer
-    counting exchange, outside the timed hot path)."""
-    import torch.distributed as dist
-    if group is None and not (dist.is_available() and dist.is_initialized()):
-        return codes, counts
-    world = dist.get_world_size(group)
-    if world == 1:
-        return codes, counts
-    n = torch.tensor([codes.numel()], dtype=torch.int64, device=codes.device)
-    ns = torch.zeros(world, dtype=torch.int64, device=codes.device)
-    dist.all_gather_into_tensor(ns, n, group=group)
-    nmax = int(ns.max())
-    pad = torch.zeros(2, nmax, dtype=torch.int64, device=codes.device)
-    pad[0, : codes.numel()] = codes
-    pad[1, : codes.numel()] = counts
-    out = torch.empty(world, 2, nmax, dtype=torch.int64, device=codes.device)
-    dist.all_gather_into_tensor(out, pad, group=group)
-    cs = torch.cat([out[r, 0, : int(ns[r])] for r in range(world)])
-    ct = torch.cat([out[r, 1, : int(ns[r])] for r in range(world)])
-    u, inv = torch.unique(cs, return_inverse=True)
-    tot = torch.zeros_like(u).scatter_add_(0, inv, ct)
-    return u, tot
-
-
 def library_from_counts(codes: torch.Tensor, counts: torch.Tensor, k: int, min_mult: int, seed: int) -> KmerLibrary:
     keep = counts >= min_mult
     codes, counts = codes[keep], counts[keep]
