@@ -68,6 +68,7 @@ struct TcParams {
     int64_t db_tiles, q_tiles, units;   // units = (groups of `pair + 1` query tiles) x database tiles
     int n_ctas, slots, klo, khi;        // n_ctas = persistent workers (CTAs, or CTA pairs when pair == 1)
     int pair;                           // 1: cta_group::2 -- two CTAs share every database tile (M = 256 per MMA)
+    int sparse_max;                     // a warp takes the max-first filter after a tile with at most this many hits
     unsigned long long *keys;
     int *counts;
     float *thrs;
@@ -664,7 +665,7 @@ fr_knn_tc_kernel(const __grid_constant__ CUtensorMap tmap, const TcParams p) {
                     n_hitmax += __reduce_max_sync(0xFFFFFFFFu, dh);
                 }
                 // the next tile takes the max-first filter when this one had at most a hit per chunk
-                sparse_next = __reduce_add_sync(0xFFFFFFFFu, mycnt - cnt_at_tile_start) <= TC_N / TC_CH / TC_EPQ;
+                sparse_next = __reduce_add_sync(0xFFFFFFFFu, mycnt - cnt_at_tile_start) <= p.sparse_max;
                 s_cnt[sub * TC_M + row_in_tile] = mycnt;
                 __syncwarp();
                 if (lane == 0) {
@@ -1048,6 +1049,8 @@ int tc_setup(fr_ctx *ctx, TcSetup &S, const void *d_Eh, const float *d_norms, in
     // threshold stays tight (hits per row grow with the kept count)
     p.klo = k + 30;
     p.khi = p.klo + 48;
+    p.sparse_max = TC_N / TC_CH / TC_EPQ;                        // one hit per chunk of the warp
+    if (const char *e = getenv("FR_KNN_SPARSE_MAX")) p.sparse_max = atoi(e);   // tuning experiments only
     if (const char *e = getenv("FR_KNN_KLO")) p.klo = atoi(e);   // tuning experiments only
     if (const char *e = getenv("FR_KNN_KHI")) p.khi = atoi(e);
     p.norms = d_norms;
