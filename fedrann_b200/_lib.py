@@ -22,6 +22,7 @@ SYMBOLS = [
     "fr_library_parse", "fr_fastx_parse", "fr_write_output_bin", "fr_write_frequency_bin", "fr_read_output_bin",
     "fr_table_build", "fr_table_set_sampler", "fr_extract_count", "fr_extract_fill", "fr_extract_async", "fr_project", "fr_normalize",
     "fr_knn", "fr_knn_rows_ready_after", "fr_knn_last_fallback_rows", "fr_knn_last_path",
+    "fr_knn_exact_noalloc",
     "fr_knn_inc_begin", "fr_knn_inc_phase", "fr_knn_inc_finish",
     "fr_kmer_count_begin", "fr_kmer_count_add", "fr_kmer_count_export", "fr_write_overlaps_tsv",
     "fr_exchange_create", "fr_exchange_connect", "fr_exchange_rows_f32", "fr_exchange_rows_f16", "fr_exchange_norms",
@@ -87,6 +88,8 @@ def lib():
     L.fr_knn_last_fallback_rows.restype = i64
     L.fr_knn_last_path.argtypes = [vp]
     L.fr_knn_last_path.restype = i32
+    L.fr_knn_exact_noalloc.argtypes = [vp, vp, vp, i64, i32, i64, i64, i32, vp, vp, vp]
+    L.fr_knn_exact_noalloc.restype = i32
     u64 = C.c_uint64
     L.fr_table_set_sampler.argtypes = [vp, u64, u64, vp]
     L.fr_kmer_count_begin.argtypes = [vp, i32, i64, vp]

@@ -171,6 +171,19 @@ int64_t fr_knn_last_fallback_rows(fr_ctx *ctx);
 /* which path the last fr_knn / fr_knn_inc_begin took: 0 = tensor-core pass + fp32 re-rank, 1 = fp32 scan on the
  * CUDA cores (mode 1, or a shape outside the tensor-core path: D > 512, k > 128, n_db < 2k); -1 before any call */
 int fr_knn_last_path(const fr_ctx *ctx);
+/* Exact fp32 cosine kNN that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same result as fr_knn mode 1 (d_Eh is not needed): d_idx i32[nq,k], d_dist f32[nq,k],
+ * ascending distance, ties by lower index; with fewer than k database rows the tail is idx -1 / dist +inf.
+ * Its scratch -- one 64-bit key per (query, database row) -- is a file-scope static __device__ array of
+ * 2 097 152 keys (16 MiB) that every GPU which loads the library holds until exit.  Limits, FR_ERR_ARG with a
+ * message beyond them: nq * n_db <= 2 097 152, nq <= 4096, D <= 1024, 1 <= k <= 128.  The call makes no
+ * cudaMalloc / cudaFree and uses no allocating library routine; the first call on a device resolves the array's
+ * address (cudaGetSymbolAddress), so make one call before starting a graph capture.  All calls share the array:
+ * nothing in it must start at zero (a call reads only the keys it wrote itself), but calls that overlap on one
+ * GPU -- two streams, two threads -- race on it; serialise them.  Asynchronous on `stream`. */
+int fr_knn_exact_noalloc(fr_ctx *ctx, const float *d_En, const float *d_norms, int64_t n_db, int D, int64_t q0,
+                         int64_t nq, int k, int32_t *d_idx, float *d_dist, void *stream);
 
 /* ---- multi-GPU: the embedding database exchanged through peer memory (NVLink), one rank per GPU ----
  * reads shard over the GPUs, each GPU searches its query rows against ALL rows.  The reference
