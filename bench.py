@@ -497,6 +497,7 @@ def main():
 
     n_warm = max(args.warmup, 3)
     progress("table and projection uploaded; warm-up")
+    sync_all()      # ranks enter the first exchange together (its flag barrier has a 60 s watchdog)
     for i in range(n_warm):
         res = device_step()
         if i == 0:
